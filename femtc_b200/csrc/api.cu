@@ -1,0 +1,729 @@
+// C ABI of libfemtc_b200.so (declared in include/femtc_b200.h): argument validation in the
+// reference's own order, dispatch between the tiled TMA kernels and the generic kernels, and
+// the host-pointer path (chunked, pipelined H2D -> kernel -> D2H).
+#include "common.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace femtc
+{
+
+// ---- error state ---------------------------------------------------------------------------
+static thread_local std::string t_last_error;
+void set_error(const std::string& msg) { t_last_error = msg; }
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line)
+{
+  char buf[512];
+  std::snprintf(buf, sizeof buf, "CUDA error %d (%s) in %s at %s:%d", (int)e, cudaGetErrorString(e),
+                what, file, line);
+  set_error(buf);
+  std::fprintf(stderr, "femtc_b200: %s\n", buf);
+  (void)cudaGetLastError(); // clear non-sticky errors
+  return FEMTC_ERR_CUDA;
+}
+
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- options ---------------------------------------------------------------------------------
+static std::atomic<long long> g_opt_kernel{0};
+static std::atomic<long long> g_opt_host_chunk_mb{64};
+static std::atomic<long long> g_opt_variant{0};
+
+long long opt_variant() { return g_opt_variant.load(); }
+
+// ---- device bookkeeping ---------------------------------------------------------------------
+static int g_sm_count[64];
+static int g_usable_devices = -1;
+static std::once_flag g_probe_once;
+
+static void probe_devices()
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess)
+  {
+    (void)cudaGetLastError();
+    n = 0;
+  }
+  int usable = 0;
+  for (int d = 0; d < n && d < 64; ++d)
+  {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, d) != cudaSuccess)
+      break;
+    if (p.major != 10) // the library holds sm_100a code only
+      break;
+    g_sm_count[d] = p.multiProcessorCount;
+    ++usable;
+  }
+  g_usable_devices = usable;
+}
+
+static int require_device()
+{
+  std::call_once(g_probe_once, probe_devices);
+  if (g_usable_devices <= 0)
+  {
+    set_error("no usable sm_100 (B200) device: libfemtc_b200 has no CPU fallback");
+    return FEMTC_ERR_CUDA;
+  }
+  return FEMTC_OK;
+}
+
+int sm_count()
+{
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64 || g_sm_count[d] == 0)
+    return 148;
+  return g_sm_count[d];
+}
+
+// ---- validation, in the order the reference dispatches (Nb, Mb, order, degree) ----------------
+static int check_knobs(int degree, int order, int Mb, int Nb)
+{
+  auto ok_block = [](int b) { return b == 0 || b == 4 || b == 8 || b == 16; };
+  if (!ok_block(Nb) || !ok_block(Mb))
+  {
+    set_error("Block size not supported");
+    return FEMTC_ERR_BLOCK;
+  }
+  if (order < 0 || order > 5)
+  {
+    set_error("order not supported");
+    return FEMTC_ERR_ORDER;
+  }
+  if (degree < 1 || degree > 25)
+  {
+    set_error("degree not supported");
+    return FEMTC_ERR_DEGREE;
+  }
+  return FEMTC_OK;
+}
+
+// ---- device-pointer operators --------------------------------------------------------------------
+template <typename T>
+static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T* ddetJ,
+                       size_t num_cells, int degree, cudaStream_t stream)
+{
+  if (degree < 1 || degree > 25)
+  {
+    set_error("degree not supported");
+    return FEMTC_ERR_DEGREE;
+  }
+  const size_t n2 = (size_t)(degree + 1) * (degree + 1);
+  if (!phi || (num_cells && (!dU || !dW || !ddetJ)))
+  {
+    set_error("null pointer argument");
+    return FEMTC_ERR_ARG;
+  }
+  if (phi_len < n2)
+  {
+    set_error("phi shorter than (degree+1)^2");
+    return FEMTC_ERR_LENGTH;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  MassArgs<T> a{phi, dU, dW, ddetJ, num_cells, degree, stream};
+  size_t done = 0;
+  const long long force = g_opt_kernel.load();
+  if (force != 1 && degree <= 8)
+  {
+    const long long n = launch_mass_tiled<T>(a);
+    if (n < 0)
+      return (int)-n;
+    done = (size_t)n;
+    if (force == 2 && done == 0 && num_cells)
+    {
+      set_error("tiled kernel forced but not applicable (alignment or size)");
+      return FEMTC_ERR_ARG;
+    }
+  }
+  if (done < num_cells)
+  {
+    const size_t nd = n2 * (degree + 1);
+    MassArgs<T> t{phi, dU + done * nd, dW + done * nd, ddetJ + done * nd, num_cells - done, degree, stream};
+    rc = launch_mass_generic<T>(t);
+  }
+  return rc;
+}
+
+static std::once_flag g_short_phi_once;
+
+template <typename T>
+static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T* dG,
+                            size_t num_cells, int degree, int mode, cudaStream_t stream)
+{
+  if (degree < 1 || degree > 25)
+  {
+    set_error("degree not supported");
+    return FEMTC_ERR_DEGREE;
+  }
+  if (mode != FEMTC_STIFFNESS_REF_EXACT && mode != FEMTC_STIFFNESS_FULL)
+  {
+    set_error("unknown stiffness mode");
+    return FEMTC_ERR_MODE;
+  }
+  const size_t n2 = (size_t)(degree + 1) * (degree + 1);
+  if (!phi || (num_cells && (!dU || !dW || !dG)))
+  {
+    set_error("null pointer argument");
+    return FEMTC_ERR_ARG;
+  }
+  if (phi_len < n2)
+  {
+    set_error("phi shorter than (degree+1)^2");
+    return FEMTC_ERR_LENGTH;
+  }
+  const T* A = phi;
+  const T* D = phi + n2;
+  if (phi_len < 2 * n2)
+  {
+    // bench_stiffness.cpp:74 allocates (p+1)^2 values but stiffness.hpp:45 reads the derivative
+    // matrix from phi[(p+1)^2 ...): never read past what the caller gave us.
+    std::call_once(g_short_phi_once, [] {
+      std::fprintf(stderr, "femtc_b200: stiffness called with phi of (P+1)^2 values; the operator needs "
+                           "2(P+1)^2 = [basis | derivative]. Using derivative := basis (no out-of-bounds read).\n");
+    });
+    D = A;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  StiffnessArgs<T> a{A, D, dU, dW, dG, num_cells, degree, mode, stream};
+  size_t done = 0;
+  const long long force = g_opt_kernel.load();
+  if (force != 1 && degree <= 8)
+  {
+    const long long n = launch_stiffness_tiled<T>(a);
+    if (n < 0)
+      return (int)-n;
+    done = (size_t)n;
+    if (force == 2 && done == 0 && num_cells)
+    {
+      set_error("tiled kernel forced but not applicable (alignment or size)");
+      return FEMTC_ERR_ARG;
+    }
+  }
+  if (done < num_cells)
+  {
+    const size_t nd = n2 * (degree + 1);
+    StiffnessArgs<T> t{A, D, dU + done * nd, dW + done * nd, dG + done * nd * 6, num_cells - done, degree, mode, stream};
+    rc = launch_stiffness_generic<T>(t);
+  }
+  return rc;
+}
+
+// ---- host-pointer path: chunked three-deep pipeline ------------------------------------------------
+// Each slot owns a stream and device buffers for one chunk of cells.  Per chunk:
+//   H2D(U), H2D(detJ|G) -> operator kernel -> D2H(W), all on the slot's stream, so chunk i+1's
+// uploads and chunk i-1's download overlap chunk i's kernel (separate copy engines per direction).
+// Page-locked caller buffers (femtc_host_alloc / cudaHostAlloc / cudaHostRegister) are DMA'd in
+// place; pageable buffers go through the driver's staging path.
+struct Slot
+{
+  cudaStream_t stream = nullptr;
+  void* dU = nullptr;
+  void* dG = nullptr;
+  void* dW = nullptr;
+  size_t capU = 0, capG = 0, capW = 0;
+};
+
+struct DeviceCache
+{
+  std::mutex mu;
+  Slot slots[3];
+  bool streams_ready = false;
+};
+static DeviceCache g_cache[64];
+
+static int ensure(void*& p, size_t& cap, size_t bytes)
+{
+  if (cap >= bytes)
+    return FEMTC_OK;
+  if (p)
+    FEMTC_CUDA(cudaFree(p));
+  p = nullptr;
+  cap = 0;
+  FEMTC_CUDA(cudaMalloc(&p, bytes));
+  cap = bytes;
+  return FEMTC_OK;
+}
+
+template <typename T, typename Launch>
+static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t num_cells, size_t nd,
+                         Launch&& launch)
+{
+  int dev = 0;
+  FEMTC_CUDA(cudaGetDevice(&dev));
+  DeviceCache& cache = g_cache[dev];
+  std::lock_guard<std::mutex> lock(cache.mu);
+  if (!cache.streams_ready)
+  {
+    for (auto& s : cache.slots)
+      FEMTC_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    cache.streams_ready = true;
+  }
+  const size_t bytes_per_cell = nd * sizeof(T) * (1 + geom_width);
+  size_t chunk_cells = std::max<size_t>(1, ((size_t)g_opt_host_chunk_mb.load() << 20) / bytes_per_cell);
+  // keep chunk boundaries 16-byte aligned in every array so the TMA path applies to all chunks
+  chunk_cells = std::max<size_t>(16, chunk_cells & ~size_t(15));
+  chunk_cells = std::min(chunk_cells, std::max<size_t>(num_cells, 1));
+
+  int rc = FEMTC_OK;
+  size_t i = 0;
+  for (size_t c0 = 0; c0 < num_cells && rc == FEMTC_OK; c0 += chunk_cells, ++i)
+  {
+    const size_t n = std::min(chunk_cells, num_cells - c0);
+    Slot& s = cache.slots[i % 3];
+    // the slot's previous chunk (three chunks ago) must have drained before its buffers are reused
+    FEMTC_CUDA(cudaStreamSynchronize(s.stream));
+    if ((rc = ensure(s.dU, s.capU, chunk_cells * nd * sizeof(T))))
+      break;
+    if ((rc = ensure(s.dG, s.capG, chunk_cells * nd * geom_width * sizeof(T))))
+      break;
+    if ((rc = ensure(s.dW, s.capW, chunk_cells * nd * sizeof(T))))
+      break;
+    FEMTC_CUDA(cudaMemcpyAsync(s.dU, U + c0 * nd, n * nd * sizeof(T), cudaMemcpyHostToDevice, s.stream));
+    FEMTC_CUDA(cudaMemcpyAsync(s.dG, geom + c0 * nd * geom_width, n * nd * geom_width * sizeof(T),
+                               cudaMemcpyHostToDevice, s.stream));
+    rc = launch((const T*)s.dU, (T*)s.dW, (const T*)s.dG, n, s.stream);
+    if (rc)
+      break;
+    FEMTC_CUDA(cudaMemcpyAsync(W + c0 * nd, s.dW, n * nd * sizeof(T), cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (auto& s : cache.slots)
+  {
+    cudaError_t e = cudaStreamSynchronize(s.stream);
+    if (e != cudaSuccess && rc == FEMTC_OK)
+      rc = cuda_fail(e, "cudaStreamSynchronize(slot)", __FILE__, __LINE__);
+  }
+  return rc;
+}
+
+template <typename T>
+static int mass_host(const T* phi, size_t phi_len, const T* U, T* W, const T* detJ, size_t num_cells,
+                     int degree, int order, int Mb, int Nb)
+{
+  int rc = check_knobs(degree, order, Mb, Nb);
+  if (rc)
+    return rc;
+  const size_t n1 = degree + 1;
+  if (!phi || (num_cells && (!U || !W || !detJ)))
+  {
+    set_error("null pointer argument");
+    return FEMTC_ERR_ARG;
+  }
+  if (phi_len < n1 * n1)
+  {
+    set_error("phi shorter than (degree+1)^2");
+    return FEMTC_ERR_LENGTH;
+  }
+  if ((rc = require_device()))
+    return rc;
+  if (num_cells == 0)
+    return FEMTC_OK;
+  return host_pipeline<T>(U, W, detJ, 1, num_cells, n1 * n1 * n1,
+                          [&](const T* dU, T* dW, const T* dJ, size_t n, cudaStream_t s)
+                          { return mass_device<T>(phi, phi_len, dU, dW, dJ, n, degree, s); });
+}
+
+template <typename T>
+static int stiffness_host(const T* phi, size_t phi_len, const T* U, T* W, const T* G, size_t num_cells,
+                          int degree, int order, int Mb, int Nb, int mode)
+{
+  int rc = check_knobs(degree, order, Mb, Nb);
+  if (rc)
+    return rc;
+  if (mode != FEMTC_STIFFNESS_REF_EXACT && mode != FEMTC_STIFFNESS_FULL)
+  {
+    set_error("unknown stiffness mode");
+    return FEMTC_ERR_MODE;
+  }
+  const size_t n1 = degree + 1;
+  if (!phi || (num_cells && (!U || !W || !G)))
+  {
+    set_error("null pointer argument");
+    return FEMTC_ERR_ARG;
+  }
+  if (phi_len < n1 * n1)
+  {
+    set_error("phi shorter than (degree+1)^2");
+    return FEMTC_ERR_LENGTH;
+  }
+  if ((rc = require_device()))
+    return rc;
+  if (num_cells == 0)
+    return FEMTC_OK;
+  return host_pipeline<T>(U, W, G, 6, num_cells, n1 * n1 * n1,
+                          [&](const T* dU, T* dW, const T* dG, size_t n, cudaStream_t s)
+                          { return stiffness_device<T>(phi, phi_len, dU, dW, dG, n, degree, mode, s); });
+}
+
+// ---- small host-pointer helpers for the GEMM / contraction entry points ----------------------------
+struct DevBuf
+{
+  void* p = nullptr;
+  ~DevBuf()
+  {
+    if (p)
+      cudaFree(p);
+  }
+  int alloc(size_t bytes)
+  {
+    FEMTC_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 16)));
+    return FEMTC_OK;
+  }
+  int upload(const void* h, size_t bytes)
+  {
+    int rc = alloc(bytes);
+    if (rc)
+      return rc;
+    FEMTC_CUDA(cudaMemcpy(p, h, bytes, cudaMemcpyHostToDevice));
+    return FEMTC_OK;
+  }
+};
+
+template <typename T>
+static int gemm_blocked_host(int k, int m, int n, int order, int MB, int NB, const T* a, const T* b, T* c)
+{
+  if (k < 1 || m < 1 || n < 1 || MB < 0 || NB < 0 || !a || !b || !c)
+  {
+    set_error("bad gemm_blocked shape or null pointer");
+    return FEMTC_ERR_ARG;
+  }
+  if (order < 0 || order > 5)
+  {
+    set_error("order not supported");
+    return FEMTC_ERR_ORDER;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  DevBuf dA, dB, dC;
+  if ((rc = dA.upload(a, sizeof(T) * m * k)) || (rc = dB.upload(b, sizeof(T) * k * n)) ||
+      (rc = dC.alloc(sizeof(T) * m * n)))
+    return rc;
+  if ((rc = launch_gemm_blocked<T>(k, m, n, (const T*)dA.p, (const T*)dB.p, (T*)dC.p, nullptr)))
+    return rc;
+  FEMTC_CUDA(cudaMemcpy(c, dC.p, sizeof(T) * m * n, cudaMemcpyDeviceToHost));
+  return FEMTC_OK;
+}
+
+template <typename T>
+static int gemm_strided_host(int k, int m, int nc, int sai, int sap, int sbp, int sbj, int ldc, const T* a,
+                             const T* b, T* c)
+{
+  if (k < 1 || m < 1 || nc < 1 || sai < 1 || sap < 1 || sbp < 1 || sbj < 1 || ldc < nc || !a || !b || !c)
+  {
+    set_error("bad strided gemm shape or null pointer");
+    return FEMTC_ERR_ARG;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  // extents actually touched
+  const size_t na = (size_t)(m - 1) * sai + (size_t)(k - 1) * sap + 1;
+  const size_t nb = (size_t)(k - 1) * sbp + (size_t)(nc - 1) * sbj + 1;
+  const size_t ncc = (size_t)(m - 1) * ldc + nc;
+  DevBuf dA, dB, dC;
+  if ((rc = dA.upload(a, sizeof(T) * na)) || (rc = dB.upload(b, sizeof(T) * nb)) ||
+      (rc = dC.upload(c, sizeof(T) * ncc)))
+    return rc;
+  if ((rc = launch_gemm_strided<T>(k, m, nc, sai, sap, sbp, sbj, ldc, (const T*)dA.p, (const T*)dB.p, (T*)dC.p,
+                                   nullptr)))
+    return rc;
+  // copy back row by row so that the gaps between rows of c (ldc > nc) keep the caller's values
+  FEMTC_CUDA(cudaMemcpy2D(c, sizeof(T) * ldc, dC.p, sizeof(T) * ldc, sizeof(T) * nc, m, cudaMemcpyDeviceToHost));
+  return FEMTC_OK;
+}
+
+template <typename T>
+static int gemm_micro_host(int k, int m, int nc, int lda, int ldb, int ldc, int order, const T* a,
+                           const T* b, T* c)
+{
+  if (k < 1 || m < 1 || nc < 1 || lda < m || ldb < nc || ldc < nc)
+  {
+    set_error("bad gemm_micro shape");
+    return FEMTC_ERR_ARG;
+  }
+  if (order < 0 || order > 5)
+  {
+    set_error("order not supported");
+    return FEMTC_ERR_ORDER;
+  }
+  return gemm_strided_host<T>(k, m, nc, 1, lda, ldb, 1, ldc, a, b, c);
+}
+
+template <typename T>
+static int apply_contractions_host(int Na, int Nb, int Tr, const T* I0, const T* I1, const T* I2,
+                                   const T* B, T* A, size_t batch)
+{
+  if (Na < 1 || Nb < 1 || Na > 64 || Nb > 64 || !I0 || !I1 || !I2 || (batch && (!A || !B)))
+  {
+    set_error("bad apply_contractions shape or null pointer");
+    return FEMTC_ERR_ARG;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  if (batch == 0)
+    return FEMTC_OK;
+  const size_t nm = (size_t)Na * Nb, nb3 = (size_t)Nb * Nb * Nb, na3 = (size_t)Na * Na * Na;
+  DevBuf d0, d1, d2, dB, dA;
+  if ((rc = d0.upload(I0, sizeof(T) * nm)) || (rc = d1.upload(I1, sizeof(T) * nm)) ||
+      (rc = d2.upload(I2, sizeof(T) * nm)) || (rc = dB.upload(B, sizeof(T) * nb3 * batch)) ||
+      (rc = dA.alloc(sizeof(T) * na3 * batch)))
+    return rc;
+  if ((rc = launch_apply_contractions<T>(Na, Nb, Tr, (const T*)d0.p, (const T*)d1.p, (const T*)d2.p,
+                                         (const T*)dB.p, (T*)dA.p, batch, nullptr)))
+    return rc;
+  FEMTC_CUDA(cudaMemcpy(A, dA.p, sizeof(T) * na3 * batch, cudaMemcpyDeviceToHost));
+  return FEMTC_OK;
+}
+
+} // namespace femtc
+
+// ================================ extern "C" =====================================================
+using namespace femtc;
+
+extern "C"
+{
+
+int femtc_mass_apply_f64(const double* phi, size_t phi_len, const double* U, double* W, const double* detJ,
+                         size_t num_cells, int degree, int order, int Mb, int Nb)
+{
+  return mass_host<double>(phi, phi_len, U, W, detJ, num_cells, degree, order, Mb, Nb);
+}
+int femtc_mass_apply_f32(const float* phi, size_t phi_len, const float* U, float* W, const float* detJ,
+                         size_t num_cells, int degree, int order, int Mb, int Nb)
+{
+  return mass_host<float>(phi, phi_len, U, W, detJ, num_cells, degree, order, Mb, Nb);
+}
+int femtc_stiffness_apply_f64(const double* phi, size_t phi_len, const double* U, double* W, const double* G,
+                              size_t num_cells, int degree, int order, int Mb, int Nb, int mode)
+{
+  return stiffness_host<double>(phi, phi_len, U, W, G, num_cells, degree, order, Mb, Nb, mode);
+}
+int femtc_stiffness_apply_f32(const float* phi, size_t phi_len, const float* U, float* W, const float* G,
+                              size_t num_cells, int degree, int order, int Mb, int Nb, int mode)
+{
+  return stiffness_host<float>(phi, phi_len, U, W, G, num_cells, degree, order, Mb, Nb, mode);
+}
+
+int femtc_mass_apply_device_f64(const double* phi, size_t phi_len, const double* dU, double* dW,
+                                const double* ddetJ, size_t num_cells, int degree, void* stream)
+{
+  return mass_device<double>(phi, phi_len, dU, dW, ddetJ, num_cells, degree, (cudaStream_t)stream);
+}
+int femtc_mass_apply_device_f32(const float* phi, size_t phi_len, const float* dU, float* dW,
+                                const float* ddetJ, size_t num_cells, int degree, void* stream)
+{
+  return mass_device<float>(phi, phi_len, dU, dW, ddetJ, num_cells, degree, (cudaStream_t)stream);
+}
+int femtc_stiffness_apply_device_f64(const double* phi, size_t phi_len, const double* dU, double* dW,
+                                     const double* dG, size_t num_cells, int degree, int mode, void* stream)
+{
+  return stiffness_device<double>(phi, phi_len, dU, dW, dG, num_cells, degree, mode, (cudaStream_t)stream);
+}
+int femtc_stiffness_apply_device_f32(const float* phi, size_t phi_len, const float* dU, float* dW,
+                                     const float* dG, size_t num_cells, int degree, int mode, void* stream)
+{
+  return stiffness_device<float>(phi, phi_len, dU, dW, dG, num_cells, degree, mode, (cudaStream_t)stream);
+}
+
+int femtc_gemm_blocked_f64(int k, int m, int n, int order, int MB, int NB, const double* a, const double* b, double* c)
+{
+  return gemm_blocked_host<double>(k, m, n, order, MB, NB, a, b, c);
+}
+int femtc_gemm_blocked_f32(int k, int m, int n, int order, int MB, int NB, const float* a, const float* b, float* c)
+{
+  return gemm_blocked_host<float>(k, m, n, order, MB, NB, a, b, c);
+}
+int femtc_gemm_micro_f64(int k, int m, int nc, int lda, int ldb, int ldc, int order, const double* a,
+                         const double* b, double* c)
+{
+  return gemm_micro_host<double>(k, m, nc, lda, ldb, ldc, order, a, b, c);
+}
+int femtc_gemm_micro_f32(int k, int m, int nc, int lda, int ldb, int ldc, int order, const float* a,
+                         const float* b, float* c)
+{
+  return gemm_micro_host<float>(k, m, nc, lda, ldb, ldc, order, a, b, c);
+}
+int femtc_gemm_strided_acc_f64(int k, int m, int nc, int sai, int sap, int sbp, int sbj, int ldc, const double* a,
+                               const double* b, double* c)
+{
+  return gemm_strided_host<double>(k, m, nc, sai, sap, sbp, sbj, ldc, a, b, c);
+}
+int femtc_gemm_strided_acc_f32(int k, int m, int nc, int sai, int sap, int sbp, int sbj, int ldc, const float* a,
+                               const float* b, float* c)
+{
+  return gemm_strided_host<float>(k, m, nc, sai, sap, sbp, sbj, ldc, a, b, c);
+}
+int femtc_apply_contractions_f64(int Na, int Nb, int Tr, const double* I0, const double* I1, const double* I2,
+                                 const double* B, double* A, size_t batch)
+{
+  return apply_contractions_host<double>(Na, Nb, Tr, I0, I1, I2, B, A, batch);
+}
+int femtc_apply_contractions_f32(int Na, int Nb, int Tr, const float* I0, const float* I1, const float* I2,
+                                 const float* B, float* A, size_t batch)
+{
+  return apply_contractions_host<float>(Na, Nb, Tr, I0, I1, I2, B, A, batch);
+}
+
+int femtc_string2order(const char* name)
+{
+  static const char* names[6] = {"ijk", "ikj", "jik", "jki", "kij", "kji"};
+  if (!name)
+    return -1;
+  for (int i = 0; i < 6; ++i)
+    if (std::strcmp(name, names[i]) == 0)
+      return i;
+  return -1;
+}
+
+int femtc_checksum_device_f64(const double* dX, size_t n, double* d_out4, void* stream)
+{
+  int rc = require_device();
+  return rc ? rc : launch_checksum<double>(dX, n, d_out4, (cudaStream_t)stream);
+}
+int femtc_checksum_device_f32(const float* dX, size_t n, double* d_out4, void* stream)
+{
+  int rc = require_device();
+  return rc ? rc : launch_checksum<float>(dX, n, d_out4, (cudaStream_t)stream);
+}
+int femtc_fill_uniform_device_f64(double* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
+                                  int centred, void* stream)
+{
+  int rc = require_device();
+  return rc ? rc : launch_fill_uniform<double>(dX, n, seed, stream_id, offset, centred, (cudaStream_t)stream);
+}
+int femtc_fill_uniform_device_f32(float* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
+                                  int centred, void* stream)
+{
+  int rc = require_device();
+  return rc ? rc : launch_fill_uniform<float>(dX, n, seed, stream_id, offset, centred, (cudaStream_t)stream);
+}
+
+int femtc_device_count(void)
+{
+  std::call_once(g_probe_once, probe_devices);
+  return g_usable_devices;
+}
+int femtc_set_device(int device)
+{
+  int rc = require_device();
+  if (rc)
+    return rc;
+  if (device < 0 || device >= g_usable_devices)
+  {
+    set_error("device index out of range");
+    return FEMTC_ERR_ARG;
+  }
+  FEMTC_CUDA(cudaSetDevice(device));
+  return FEMTC_OK;
+}
+int femtc_get_device(void)
+{
+  int d = -1;
+  if (require_device() || cudaGetDevice(&d) != cudaSuccess)
+    return -1;
+  return d;
+}
+const char* femtc_last_error(void) { return t_last_error.c_str(); }
+const char* femtc_version(void) { return "femtc_b200 0.1 (sm_100a)"; }
+
+void* femtc_host_alloc(size_t bytes)
+{
+  void* p = nullptr;
+  if (require_device())
+    return nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess)
+  {
+    (void)cudaGetLastError();
+    set_error("cudaHostAlloc failed");
+    return nullptr;
+  }
+  return p;
+}
+void femtc_host_free(void* p)
+{
+  if (p)
+    cudaFreeHost(p);
+}
+void femtc_release_cache(void)
+{
+  int cur = 0;
+  if (g_usable_devices <= 0 || cudaGetDevice(&cur) != cudaSuccess)
+    return;
+  for (int d = 0; d < g_usable_devices; ++d)
+  {
+    DeviceCache& c = g_cache[d];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (!c.streams_ready)
+      continue;
+    cudaSetDevice(d);
+    for (auto& s : c.slots)
+    {
+      cudaStreamSynchronize(s.stream);
+      cudaFree(s.dU);
+      cudaFree(s.dG);
+      cudaFree(s.dW);
+      s.dU = s.dG = s.dW = nullptr;
+      s.capU = s.capG = s.capW = 0;
+    }
+  }
+  cudaSetDevice(cur);
+}
+
+int femtc_set_option(const char* name, long long value)
+{
+  if (!name)
+    return FEMTC_ERR_ARG;
+  if (!std::strcmp(name, "kernel") && value >= 0 && value <= 2)
+    g_opt_kernel = value;
+  else if (!std::strcmp(name, "host_chunk_mb") && value >= 1 && value <= 4096)
+    g_opt_host_chunk_mb = value;
+  else if (!std::strcmp(name, "variant"))
+    g_opt_variant = value;
+  else
+  {
+    set_error("unknown option or value out of range");
+    return FEMTC_ERR_ARG;
+  }
+  return FEMTC_OK;
+}
+long long femtc_get_option(const char* name)
+{
+  if (!name)
+    return -1;
+  if (!std::strcmp(name, "kernel"))
+    return g_opt_kernel;
+  if (!std::strcmp(name, "host_chunk_mb"))
+    return g_opt_host_chunk_mb;
+  if (!std::strcmp(name, "variant"))
+    return g_opt_variant;
+  if (!std::strcmp(name, "launches"))
+    return g_launches;
+  return -1;
+}
+
+int femtc_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8])
+{
+  if (!info || (op != 0 && op != 1) || (dtype_bytes != 4 && dtype_bytes != 8))
+    return FEMTC_ERR_ARG;
+  for (int i = 0; i < 8; ++i)
+    info[i] = 0;
+  if (degree < 1 || degree > 25)
+    return FEMTC_ERR_DEGREE;
+  if (degree > 8 || g_opt_kernel.load() == 1)
+    return FEMTC_OK; // generic family
+  return tiled_kernel_info(op, dtype_bytes, degree, mode, info);
+}
+
+} // extern "C"

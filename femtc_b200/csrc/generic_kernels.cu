@@ -1,0 +1,504 @@
+// Generic kernels: any degree 1..25, any pointer alignment, any cell count.
+//
+// These serve (a) degrees 9..25, which the reference dispatches (mass.hpp:83-133) but which
+// are outside the tuned range, (b) the ragged tail and unaligned inputs of the tiled
+// TMA kernels (tiled_kernels.cu), and (c) the standalone small-GEMM / tensor-contraction
+// entry points behind linalg::gemm_blocked, linalg::gemm_micro and apply_contractions.
+// One thread block owns a group of cells; the per-axis contraction is written exactly as
+// gemm_blocked defines it (linalg.hpp:101-182 with k = m = n1, n = n1^2):
+//     Y[j1,j2,i] = sum_p M(i,p) X[p,j1,j2],   M(i,p) = M[i + p*n1]
+// so three sweeps walk the three axes and come back to the natural index order.
+#include "common.cuh"
+
+namespace femtc
+{
+namespace
+{
+
+constexpr int kThreads = 256;
+
+// Y[c][j*n1 + i] = sum_p M[i + p*n1] * X[c][p*n2 + j]   for a group of `cells` cells.
+// Optional fused epilogues:  * scale[c][idx]   or   (add0 + add1) + result.
+template <typename T>
+__device__ __forceinline__ void sweep(const T* __restrict__ M, const T* X, size_t xstride, T* Y,
+                                      size_t ystride, int n1, int cells, const T* scale = nullptr,
+                                      size_t sstride = 0, const T* add0 = nullptr,
+                                      const T* add1 = nullptr, size_t astride = 0)
+{
+  const int n2 = n1 * n1, nd = n2 * n1;
+  for (int t = threadIdx.x; t < cells * nd; t += blockDim.x)
+  {
+    const int c = t / nd, idx = t - c * nd;
+    const int j = idx / n1, i = idx - j * n1;
+    const T* x = X + (size_t)c * xstride + j;
+    T acc = T(0);
+    for (int p = 0; p < n1; ++p)
+      acc = fma_t(M[i + p * n1], x[(size_t)p * n2], acc);
+    if (scale)
+      acc = acc * scale[(size_t)c * sstride + idx];
+    if (add0)
+      acc = (add0[(size_t)c * astride + idx] + add1[(size_t)c * astride + idx]) + acc;
+    Y[(size_t)c * ystride + idx] = acc;
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__device__ __forceinline__ void load_matrix(T* dst, const T* __restrict__ src, int n)
+{
+  for (int t = threadIdx.x; t < n; t += blockDim.x)
+    dst[t] = src[t];
+}
+
+// mass.hpp:10-49.  Scratch: 2 buffers of cpb*nd values, in shared memory when `ws` is null,
+// else in the global workspace slice of this block.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+mass_generic_kernel(const T* __restrict__ phi, const T* __restrict__ U, T* __restrict__ W,
+                    const T* __restrict__ detJ, size_t num_cells, int n1, int cpb, T* ws)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* A = reinterpret_cast<T*>(smem_raw);
+  const int n2 = n1 * n1;
+  const size_t nd = (size_t)n2 * n1;
+  T* b0 = ws ? ws + (size_t)blockIdx.x * 2 * cpb * nd : A + n2;
+  T* b1 = b0 + (size_t)cpb * nd;
+  load_matrix(A, phi, n2);
+  __syncthreads();
+
+  const size_t groups = (num_cells + cpb - 1) / cpb;
+  for (size_t g = blockIdx.x; g < groups; g += gridDim.x)
+  {
+    const size_t cell0 = g * cpb;
+    const int cells = (int)min((size_t)cpb, num_cells - cell0);
+    const T* u = U + cell0 * nd;
+    sweep(A, u, nd, b0, nd, n1, cells);                            // mass.hpp:36
+    sweep(A, b0, nd, b1, nd, n1, cells);                           // :37
+    sweep(A, b1, nd, b0, nd, n1, cells, detJ + cell0 * nd, nd);    // :38 and the scaling :40-41
+    sweep(A, b0, nd, b1, nd, n1, cells);                           // :45 (same matrix)
+    sweep(A, b1, nd, b0, nd, n1, cells);                           // :46
+    sweep(A, b0, nd, W + cell0 * nd, nd, n1, cells);               // :47
+  }
+}
+
+// stiffness.hpp:34-99.  Scratch: 5 buffers of cpb*nd values.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+stiffness_generic_kernel(const T* __restrict__ phiA, const T* __restrict__ phiD,
+                         const T* __restrict__ U, T* __restrict__ W, const T* __restrict__ G,
+                         size_t num_cells, int n1, int cpb, int mode, T* ws)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* A = reinterpret_cast<T*>(smem_raw);
+  const int n2 = n1 * n1;
+  T* D = A + n2;
+  const size_t nd = (size_t)n2 * n1;
+  const size_t bs = (size_t)cpb * nd;
+  T* t0 = ws ? ws + (size_t)blockIdx.x * 5 * bs : D + n2;
+  T* t1 = t0 + bs;
+  T* wx = t1 + bs;
+  T* wy = wx + bs;
+  T* wz = wy + bs;
+  load_matrix(A, phiA, n2);
+  load_matrix(D, phiD, n2);
+  __syncthreads();
+
+  const size_t groups = (num_cells + cpb - 1) / cpb;
+  for (size_t g = blockIdx.x; g < groups; g += gridDim.x)
+  {
+    const size_t cell0 = g * cpb;
+    const int cells = (int)min((size_t)cpb, num_cells - cell0);
+    const T* u = U + cell0 * nd;
+    T* w = W + cell0 * nd;
+
+    sweep(D, u, nd, t0, nd, n1, cells); // stiffness.hpp:68-70   Wx = (D x A x A) U
+    sweep(A, t0, nd, t1, nd, n1, cells);
+    sweep(A, t1, nd, wx, nd, n1, cells);
+    sweep(A, u, nd, t0, nd, n1, cells); // :72-74                Wy = (A x D x A) U
+    sweep(D, t0, nd, t1, nd, n1, cells);
+    sweep(A, t1, nd, wy, nd, n1, cells);
+    sweep(A, t0, nd, t1, nd, n1, cells); // :76-77 (REF_EXACT: no derivative)
+    sweep(mode == FEMTC_STIFFNESS_FULL ? D : A, t1, nd, wz, nd, n1, cells);
+
+    // stiffness.hpp:14-29
+    const T* g6 = G + cell0 * nd * 6;
+    for (int t = threadIdx.x; t < cells * (int)nd; t += blockDim.x)
+    {
+      const T* gq = g6 + (size_t)t * 6;
+      const T w0 = wx[t], w1 = wy[t], w2 = wz[t];
+      wx[t] = (gq[5] * w0 + gq[4] * w1 + gq[2] * w2);
+      wy[t] = (gq[4] * w0 + gq[3] * w1 + gq[1] * w2);
+      wz[t] = (gq[2] * w0 + gq[1] * w1 + gq[0] * w2);
+    }
+    __syncthreads();
+
+    if (mode == FEMTC_STIFFNESS_REF_EXACT)
+    {
+      // :95-97 is the only back-contraction whose result survives (each one assigns W)
+      sweep(A, wz, nd, t0, nd, n1, cells);
+      sweep(A, t0, nd, t1, nd, n1, cells);
+      sweep(D, t1, nd, w, nd, n1, cells);
+    }
+    else
+    {
+      sweep(D, wx, nd, t0, nd, n1, cells);
+      sweep(A, t0, nd, t1, nd, n1, cells);
+      sweep(A, t1, nd, wx, nd, n1, cells);
+      sweep(A, wy, nd, t0, nd, n1, cells);
+      sweep(D, t0, nd, t1, nd, n1, cells);
+      sweep(A, t1, nd, wy, nd, n1, cells);
+      sweep(A, wz, nd, t0, nd, n1, cells);
+      sweep(A, t0, nd, t1, nd, n1, cells);
+      sweep(D, t1, nd, w, nd, n1, cells, (const T*)nullptr, 0, wx, wy, nd);
+    }
+  }
+}
+
+// linalg.hpp:101-182: C[i + j*m] = sum_p A[i + p*m] * B[p*n + j]  (C overwritten)
+template <typename T>
+__global__ void gemm_blocked_kernel(int k, int m, int n, const T* __restrict__ A,
+                                    const T* __restrict__ B, T* __restrict__ C)
+{
+  const size_t total = (size_t)m * n;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x)
+  {
+    const int j = (int)(t / m), i = (int)(t - (size_t)j * m);
+    T acc = T(0);
+    for (int p = 0; p < k; ++p)
+      acc = fma_t(A[i + (size_t)p * m], B[(size_t)p * n + j], acc);
+    C[t] = acc;
+  }
+}
+
+// linalg.hpp:45-94 in strided form: c[i*ldc + j] += sum_p a[i*sai + p*sap] * b[p*sbp + j*sbj]
+// (accumulates, p ascending).  gemm_micro is sai=1, sap=lda, sbp=ldb, sbj=1; tmm.hpp's `contract`
+// variants (tmm.hpp:24-32, :65-85) are other stride choices.
+template <typename T>
+__global__ void gemm_strided_kernel(int k, int m, int nc, int sai, int sap, int sbp, int sbj, int ldc,
+                                    const T* __restrict__ a, const T* __restrict__ b, T* c)
+{
+  const size_t total = (size_t)m * nc;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x)
+  {
+    const int i = (int)(t / nc), j = (int)(t - (size_t)i * nc);
+    T acc = c[(size_t)i * ldc + j];
+    for (int p = 0; p < k; ++p)
+      acc = fma_t(a[(size_t)i * sai + (size_t)p * sap], b[(size_t)p * sbp + (size_t)j * sbj], acc);
+    c[(size_t)i * ldc + j] = acc;
+  }
+}
+
+// tmm.hpp:91-126, one tensor per block iteration; scratch s0 [Na,Nb,Nb], s1 [Na,Na,Nb].
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+apply_contractions_kernel(int Na, int Nb, int Tr, const T* __restrict__ I0,
+                          const T* __restrict__ I1, const T* __restrict__ I2,
+                          const T* __restrict__ B, T* __restrict__ A, size_t batch, T* ws)
+{
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const size_t na = Na, nb = Nb;
+  const size_t n0 = na * nb * nb, n1 = na * na * nb, n3 = na * na * na;
+  T* s0 = ws ? ws + (size_t)blockIdx.x * (n0 + n1) : reinterpret_cast<T*>(smem_raw);
+  T* s1 = s0 + n0;
+  auto mat = [&](const T* I, size_t a, size_t b) { return Tr ? I[a * nb + b] : I[b * na + a]; };
+  for (size_t e = blockIdx.x; e < batch; e += gridDim.x)
+  {
+    const T* Be = B + e * nb * nb * nb;
+    T* Ae = A + e * n3;
+    for (size_t t = threadIdx.x; t < n0; t += blockDim.x) // s0[a0,b1,b2]
+    {
+      const size_t a0 = t / (nb * nb), d = t - a0 * nb * nb;
+      T acc = T(0);
+      for (size_t b0 = 0; b0 < nb; ++b0)
+        acc = fma_t(mat(I0, a0, b0), Be[b0 * nb * nb + d], acc);
+      s0[t] = acc;
+    }
+    __syncthreads();
+    for (size_t t = threadIdx.x; t < n1; t += blockDim.x) // s1[a1,a0,b2]
+    {
+      const size_t a1 = t / (na * nb), r = t - a1 * na * nb, a0 = r / nb, b2 = r - a0 * nb;
+      T acc = T(0);
+      for (size_t b1 = 0; b1 < nb; ++b1)
+        acc = fma_t(mat(I1, a1, b1), s0[(a0 * nb + b1) * nb + b2], acc);
+      s1[t] = acc;
+    }
+    __syncthreads();
+    for (size_t t = threadIdx.x; t < n3; t += blockDim.x) // A[a0,a1,a2]
+    {
+      const size_t a0 = t / (na * na), r = t - a0 * na * na, a1 = r / na, a2 = r - a1 * na;
+      T acc = T(0);
+      for (size_t b2 = 0; b2 < nb; ++b2)
+        acc = fma_t(mat(I2, a2, b2), s1[(a1 * na + a0) * nb + b2], acc);
+      Ae[t] = acc;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- checksum: deterministic two-stage reduction ----------------------------------------------
+constexpr int kChecksumBlocks = 1184; // 148 SMs x 8
+__device__ double g_checksum_partials[kChecksumBlocks * 3];
+
+template <typename T>
+__global__ void __launch_bounds__(256) checksum_stage1(const T* __restrict__ x, size_t n, double* partials)
+{
+  double s = 0, s2 = 0, mx = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+  {
+    const double v = (double)x[i];
+    s += v;
+    s2 = fma(v, v, s2);
+    mx = fmax(mx, fabs(v));
+  }
+  __shared__ double sh[3][256];
+  sh[0][threadIdx.x] = s;
+  sh[1][threadIdx.x] = s2;
+  sh[2][threadIdx.x] = mx;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1)
+  {
+    if ((int)threadIdx.x < w)
+    {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + w];
+      sh[1][threadIdx.x] += sh[1][threadIdx.x + w];
+      sh[2][threadIdx.x] = fmax(sh[2][threadIdx.x], sh[2][threadIdx.x + w]);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+  {
+    partials[blockIdx.x * 3 + 0] = sh[0][0];
+    partials[blockIdx.x * 3 + 1] = sh[1][0];
+    partials[blockIdx.x * 3 + 2] = sh[2][0];
+  }
+}
+
+__global__ void __launch_bounds__(256) checksum_stage2(const double* partials, int nblocks, size_t n, double* out4)
+{
+  __shared__ double sh[3][256];
+  double s = 0, s2 = 0, mx = 0;
+  for (int i = threadIdx.x; i < nblocks; i += 256)
+  {
+    s += partials[i * 3 + 0];
+    s2 += partials[i * 3 + 1];
+    mx = fmax(mx, partials[i * 3 + 2]);
+  }
+  sh[0][threadIdx.x] = s;
+  sh[1][threadIdx.x] = s2;
+  sh[2][threadIdx.x] = mx;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1)
+  {
+    if ((int)threadIdx.x < w)
+    {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + w];
+      sh[1][threadIdx.x] += sh[1][threadIdx.x + w];
+      sh[2][threadIdx.x] = fmax(sh[2][threadIdx.x], sh[2][threadIdx.x + w]);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+  {
+    out4[0] = sh[0][0];
+    out4[1] = sh[1][0];
+    out4[2] = sh[2][0];
+    out4[3] = (double)n;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+fill_uniform_kernel(T* x, size_t n, uint64_t base, int centred)
+{
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+  {
+    const uint64_t r = splitmix64(base + i);
+    T v;
+    if constexpr (sizeof(T) == 8)
+      v = (double)(r >> 11) * 0x1.0p-53;
+    else
+      v = (float)(r >> 40) * 0x1.0p-24f;
+    x[i] = centred ? v - T(0.5) : v;
+  }
+}
+
+// shared-memory budget we are willing to request for the generic kernels
+constexpr size_t kGenericSmemMax = 160 * 1024;
+
+template <typename K>
+int opt_in_smem(K kernel, size_t bytes)
+{
+  if (bytes > 48 * 1024)
+    FEMTC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return FEMTC_OK;
+}
+
+} // namespace
+
+// ---- launchers -------------------------------------------------------------------------------------
+
+template <typename T>
+int launch_mass_generic(const MassArgs<T>& a)
+{
+  if (a.num_cells == 0)
+    return FEMTC_OK;
+  const int n1 = a.degree + 1, n2 = n1 * n1;
+  const size_t nd = (size_t)n2 * n1;
+  T* dphi = nullptr;
+  FEMTC_CUDA(cudaMallocAsync(&dphi, n2 * sizeof(T), a.stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dphi, a.phi_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+
+  int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
+  size_t smem = (n2 + 2 * cpb * nd) * sizeof(T);
+  T* ws = nullptr;
+  const size_t groups = (a.num_cells + cpb - 1) / cpb;
+  int grid = (int)min(groups, (size_t)sm_count() * 8);
+  if (smem > kGenericSmemMax)
+  {
+    cpb = 1;
+    smem = n2 * sizeof(T);
+    grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
+    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * 2 * nd * sizeof(T), a.stream));
+  }
+  int rc = opt_in_smem(mass_generic_kernel<T>, smem);
+  if (rc)
+    return rc;
+  mass_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi, a.U, a.W, a.detJ, a.num_cells, n1, cpb, ws);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  if (ws)
+    FEMTC_CUDA(cudaFreeAsync(ws, a.stream));
+  FEMTC_CUDA(cudaFreeAsync(dphi, a.stream));
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_stiffness_generic(const StiffnessArgs<T>& a)
+{
+  if (a.num_cells == 0)
+    return FEMTC_OK;
+  const int n1 = a.degree + 1, n2 = n1 * n1;
+  const size_t nd = (size_t)n2 * n1;
+  T* dphi = nullptr;
+  FEMTC_CUDA(cudaMallocAsync(&dphi, 2 * n2 * sizeof(T), a.stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dphi, a.A_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dphi + n2, a.D_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+
+  int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
+  size_t smem = (2 * n2 + 5 * cpb * nd) * sizeof(T);
+  T* ws = nullptr;
+  const size_t groups = (a.num_cells + cpb - 1) / cpb;
+  int grid = (int)min(groups, (size_t)sm_count() * 8);
+  if (smem > kGenericSmemMax)
+  {
+    cpb = 1;
+    smem = 2 * n2 * sizeof(T);
+    grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
+    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * 5 * nd * sizeof(T), a.stream));
+  }
+  int rc = opt_in_smem(stiffness_generic_kernel<T>, smem);
+  if (rc)
+    return rc;
+  stiffness_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi, dphi + n2, a.U, a.W, a.G, a.num_cells,
+                                                                n1, cpb, a.mode, ws);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  if (ws)
+    FEMTC_CUDA(cudaFreeAsync(ws, a.stream));
+  FEMTC_CUDA(cudaFreeAsync(dphi, a.stream));
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_gemm_blocked(int k, int m, int n, const T* dA, const T* dB, T* dC, cudaStream_t s)
+{
+  const size_t total = (size_t)m * n;
+  const int grid = (int)min((total + 255) / 256, (size_t)sm_count() * 8);
+  gemm_blocked_kernel<T><<<grid, 256, 0, s>>>(k, m, n, dA, dB, dC);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_gemm_strided(int k, int m, int nc, int sai, int sap, int sbp, int sbj, int ldc,
+                        const T* dA, const T* dB, T* dC, cudaStream_t s)
+{
+  const size_t total = (size_t)m * nc;
+  const int grid = (int)min((total + 255) / 256, (size_t)sm_count() * 8);
+  gemm_strided_kernel<T><<<grid, 256, 0, s>>>(k, m, nc, sai, sap, sbp, sbj, ldc, dA, dB, dC);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_apply_contractions(int Na, int Nb, int Tr, const T* dI0, const T* dI1, const T* dI2,
+                              const T* dB, T* dA, size_t batch, cudaStream_t s)
+{
+  if (batch == 0)
+    return FEMTC_OK;
+  const size_t na = Na, nb = Nb;
+  size_t smem = (na * nb * nb + na * na * nb) * sizeof(T);
+  int grid = (int)min(batch, (size_t)sm_count() * 8);
+  T* ws = nullptr;
+  if (smem > kGenericSmemMax)
+  {
+    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * smem, s));
+    smem = 0;
+  }
+  int rc = opt_in_smem(apply_contractions_kernel<T>, smem);
+  if (rc)
+    return rc;
+  apply_contractions_kernel<T><<<grid, kThreads, smem, s>>>(Na, Nb, Tr, dI0, dI1, dI2, dB, dA, batch, ws);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  if (ws)
+    FEMTC_CUDA(cudaFreeAsync(ws, s));
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_checksum(const T* dX, size_t n, double* d_out4, cudaStream_t s)
+{
+  // The partials buffer is per device and reused: calls on one device must be stream-ordered
+  // with respect to each other (they are in every use this library makes of it).
+  double* partials = nullptr;
+  FEMTC_CUDA(cudaGetSymbolAddress((void**)&partials, g_checksum_partials));
+  checksum_stage1<T><<<kChecksumBlocks, 256, 0, s>>>(dX, n, partials);
+  checksum_stage2<<<1, 256, 0, s>>>(partials, kChecksumBlocks, n, d_out4);
+  count_launch(2);
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
+                        int centred, cudaStream_t s)
+{
+  if (n == 0)
+    return FEMTC_OK;
+  const uint64_t base = seed + stream_id * 0x9E3779B97F4A7C15ull + offset;
+  const int grid = (int)min((n + 255) / 256, (size_t)sm_count() * 16);
+  fill_uniform_kernel<T><<<grid, 256, 0, s>>>(dX, n, base, centred);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+#define INSTANTIATE(T)                                                                             \
+  template int launch_mass_generic<T>(const MassArgs<T>&);                                         \
+  template int launch_stiffness_generic<T>(const StiffnessArgs<T>&);                               \
+  template int launch_gemm_blocked<T>(int, int, int, const T*, const T*, T*, cudaStream_t);        \
+  template int launch_gemm_strided<T>(int, int, int, int, int, int, int, int, const T*, const T*,  \
+                                      T*, cudaStream_t);                                           \
+  template int launch_apply_contractions<T>(int, int, int, const T*, const T*, const T*, const T*, \
+                                            T*, size_t, cudaStream_t);                             \
+  template int launch_checksum<T>(const T*, size_t, double*, cudaStream_t);                        \
+  template int launch_fill_uniform<T>(T*, size_t, uint64_t, uint64_t, uint64_t, int, cudaStream_t);
+INSTANTIATE(double)
+INSTANTIATE(float)
+
+} // namespace femtc
