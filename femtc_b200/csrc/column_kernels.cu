@@ -1,0 +1,831 @@
+// Column kernels: degrees 5..8 (n1 = 6..9) and the low-degree shapes the slab kernels of
+// tiled_kernels.cu do not cover (fp32 with odd n1, stiffness at n1 = 2).
+//
+// Work decomposition.  A block owns a *tile* of C consecutive cells and runs n1^2 threads per cell.
+// In every phase a thread holds one *column* of its cell tensor X[i0][i1][i2] in registers: all
+// values along the phase's register axis for fixed indices on the two thread axes.
+//     phase C: register axis 0, threads (i1, i2)  -- natural order, so staged U / detJ / G / W are
+//                                                     touched with consecutive lanes (coalesced)
+//     phase B: register axis 1, threads (i0, i2)
+//     phase A: register axis 2, threads (i0, i1)
+// A contraction along the register axis is a fully unrolled FMA chain whose matrix entries are
+// immediate constant-bank operands (the 1-D tables are kernel parameters).  Between phases the
+// tensor is exchanged through padded shared-memory scratch whose strides make both the writing and
+// the reading phase bank-conflict free (tools/gen_column_layouts.py -> column_layouts.cuh).
+//     mass       C -> B -> A (x detJ) -> B -> C           6 contractions, 4 exchanges   (mass.hpp:36-47)
+//     stiffness  A -> B -> C (geometry) -> C -> B -> A    REF_EXACT 9 contractions, FULL 16
+//                                                          (stiffness.hpp:68-97; shared products formed once)
+//
+// Memory pipeline.  U (and detJ) of a tile arrive by one TMA bulk copy per tile into block staging,
+// re-requested for the block's next tile right after the barrier that follows their last read.
+// G arrives through *warp-private* rings: for plane i0 the records of a warp's 32 points are
+// contiguous in HBM (one or two pieces when the warp straddles a cell boundary), so each warp runs
+// its own cp.async.bulk + mbarrier pipeline NG planes deep, across tile boundaries, with no block
+// barrier in the geometry loop.  W leaves by TMA bulk store from staging (or by coalesced stores
+// after a C-order exchange where the phase-A staging access would conflict, n1 = 4, 8).
+// Every byte of U, detJ / G and W crosses HBM exactly once.
+//
+// Semantics follow the reference as coded (REF_EXACT / FULL: include/femtc_b200.h).
+#include "column_layouts.cuh"
+#include "common.cuh"
+#include "tma.cuh"
+
+#include <algorithm>
+
+namespace femtc
+{
+long long opt_variant();
+
+namespace
+{
+constexpr int cmaxi(int a, int b) { return a > b ? a : b; }
+constexpr int up16(int bytes) { return (bytes + 15) & ~15; }
+constexpr int up128(int bytes) { return (bytes + 127) & ~127; }
+
+template <typename T, int N1>
+struct TabA
+{
+  T a[N1 * N1];
+};
+template <typename T, int N1>
+struct TabAD
+{
+  T a[N1 * N1];
+  T d[N1 * N1];
+};
+
+// ---- contractions -------------------------------------------------------------------------------------
+// One side of every contraction is shared memory (the column being read, or the column being
+// written), the other a register array.  The loop over the shared-memory side is what carries the
+// matrix index, so it may stay rolled: the matrix entries are then fetched from the kernel-parameter
+// constant bank at a *dynamic uniform* offset.  fp32 FMAs take constant-bank operands directly, so
+// the loops are fully unrolled there; fp64 FMAs need the entries in uniform registers, and a fully
+// unrolled kernel makes ptxas hoist whole matrices into (spilled) registers -- the rolled form keeps
+// the working set to one matrix row / column.  Sums run over p ascending, starting from zero
+// (0 + a*b is exact, so this equals the reference's "Ctemp = 0; Ctemp += a*b": linalg.hpp:57,128).
+template <typename T>
+struct Roll
+{
+  static constexpr int in = sizeof(T) == 8 ? 1 : 16;  // unroll factor of the shared-memory-side loop
+};
+
+// y[i] = sum_p M[i + p*N1] * buf[base + p*stride]            (shared memory -> registers)
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in(const T (&M)[N1 * N1], const T* buf, int base, int stride, T (&y)[N1])
+{
+#pragma unroll
+  for (int i = 0; i < N1; ++i)
+    y[i] = T(0);
+#pragma unroll(Roll<T>::in)
+  for (int p = 0; p < N1; ++p)
+  {
+    const T xp = buf[base + p * stride];
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      y[i] = fma_t(M[i + p * N1], xp, y[i]);
+  }
+}
+// y[i] += sum_p M[i + p*N1] * buf[base + p*stride]
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in_add(const T (&M)[N1 * N1], const T* buf, int base, int stride, T (&y)[N1])
+{
+#pragma unroll(Roll<T>::in)
+  for (int p = 0; p < N1; ++p)
+  {
+    const T xp = buf[base + p * stride];
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      y[i] = fma_t(M[i + p * N1], xp, y[i]);
+  }
+}
+// two matrices applied to the same column
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in2(const T (&Ma)[N1 * N1], const T (&Mb)[N1 * N1], const T* buf, int base,
+                                             int stride, T (&ya)[N1], T (&yb)[N1])
+{
+#pragma unroll
+  for (int i = 0; i < N1; ++i)
+    ya[i] = yb[i] = T(0);
+#pragma unroll(Roll<T>::in)
+  for (int p = 0; p < N1; ++p)
+  {
+    const T xp = buf[base + p * stride];
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+    {
+      ya[i] = fma_t(Ma[i + p * N1], xp, ya[i]);
+      yb[i] = fma_t(Mb[i + p * N1], xp, yb[i]);
+    }
+  }
+}
+// buf[base + i*stride] = sum_p M[i + p*N1] * z[p]             (registers -> shared memory)
+template <typename T, int N1>
+__device__ __forceinline__ void contract_out(const T (&M)[N1 * N1], const T (&z)[N1], T* buf, int base, int stride)
+{
+#pragma unroll(Roll<T>::in)
+  for (int i = 0; i < N1; ++i)
+  {
+    T acc = M[i] * z[0];
+#pragma unroll
+    for (int p = 1; p < N1; ++p)
+      acc = fma_t(M[i + p * N1], z[p], acc);
+    buf[base + i * stride] = acc;
+  }
+}
+// row `i` of M times a register column: sum_p M[i + p*N1] * z[p]   (i may be dynamic)
+template <typename T, int N1>
+__device__ __forceinline__ T row_dot(const T (&M)[N1 * N1], int i, const T (&z)[N1])
+{
+  T acc = M[i] * z[0];
+#pragma unroll
+  for (int p = 1; p < N1; ++p)
+    acc = fma_t(M[i + p * N1], z[p], acc);
+  return acc;
+}
+// y[i] += M[i + p*N1] * f for all i                              (p may be dynamic)
+template <typename T, int N1>
+__device__ __forceinline__ void col_axpy(const T (&M)[N1 * N1], int p, T f, T (&y)[N1])
+{
+#pragma unroll
+  for (int i = 0; i < N1; ++i)
+    y[i] = fma_t(M[i + p * N1], f, y[i]);
+}
+
+template <class X, int AXIS>
+constexpr int xstride()
+{
+  return AXIS == 0 ? X::s0 : (AXIS == 1 ? X::s1 : X::s2);
+}
+// A phase = (register axis R; tensor axes H, L behind the thread indices hi, lo).
+template <int R_, int H_, int L_>
+struct Phase
+{
+  static constexpr int R = R_, H = H_, L = L_;
+};
+
+// offset of a thread's column inside an exchange buffer with layout X, and its register stride
+template <class X, class PH>
+__device__ __forceinline__ int col_base(int c, int hi, int lo)
+{
+  return c * X::Sc + hi * xstride<X, PH::H>() + lo * xstride<X, PH::L>();
+}
+template <class X, class PH, typename T, int N1>
+__device__ __forceinline__ void col_load(const T* buf, int base, T (&x)[N1])
+{
+#pragma unroll
+  for (int r = 0; r < N1; ++r)
+    x[r] = buf[base + r * xstride<X, PH::R>()];
+}
+template <class X, class PH, typename T, int N1>
+__device__ __forceinline__ void col_store(T* buf, int base, const T (&x)[N1])
+{
+#pragma unroll
+  for (int r = 0; r < N1; ++r)
+    buf[base + r * xstride<X, PH::R>()] = x[r];
+}
+template <int N1>
+struct Nat // natural layout as an exchange layout
+{
+  static constexpr int Sc = N1 * N1 * N1, s0 = N1 * N1, s1 = N1, s2 = 1;
+};
+
+// cells per tile.  Constraints: a tile of U must be a whole number of 16-byte units (fp64: C*n1^3
+// even; fp32: C*n1^3 % 4 == 0); C*n1^2 close to a multiple of 32 keeps lanes busy.
+template <typename T, int N1>
+constexpr int default_cells()
+{
+  if (N1 == 9) return sizeof(T) == 8 ? 2 : 4;
+  if (N1 == 8) return 2;
+  if (N1 == 7) return 4;
+  if (N1 == 6) return 7;
+  if (N1 == 5) return sizeof(T) == 8 ? 10 : 8;  // slab kernel serves fp64
+  if (N1 == 4) return 8;
+  if (N1 == 3) return 28;
+  return 64;                                     // n1 = 2: 4 threads per cell
+}
+
+template <typename T, int N1, int C>
+struct ColGeom
+{
+  static constexpr int ND = N1 * N1 * N1;
+  static constexpr int N2 = N1 * N1;
+  static constexpr int ACTIVE = C * N2;
+  static constexpr int NT = (ACTIVE + 31) & ~31;
+  static constexpr int NWARPS = NT / 32;
+  static constexpr uint32_t tile_bytes = C * ND * sizeof(T);
+  static_assert(tile_bytes % 16 == 0, "a tile must be a whole number of 16-byte units");
+  using L = ColumnLayout<T, N1>;
+  using PC = Phase<0, 1, 2>;
+  using PB = Phase<1, L::hB, L::lB>;
+  using PA = Phase<2, L::hA, L::lA>;
+  // phase A reads / writes natural-layout staging directly unless that conflicts badly
+  static constexpr bool viaC = (L::stageA_wavefronts > 3 * L::stageA_ideal);
+  static constexpr int e_elems = C * cmaxi(cmaxi(L::XBC::Sc, L::XAB::Sc), cmaxi(viaC ? L::XCA::Sc : 0, ND));
+  static constexpr int e_bytes = up128(e_elems * (int)sizeof(T));
+  static constexpr int stage_bytes = up128(C * ND * (int)sizeof(T));
+};
+
+// Resident blocks per SM the register allocator is asked to allow for (__launch_bounds__): what
+// shared memory permits, but never so many that a thread gets fewer than `target_regs` registers.
+constexpr int min_blocks_for(int threads, int smem_bytes, int target_regs)
+{
+  int by_smem = (227 * 1024) / (smem_bytes + 1024);
+  int by_regs = 65536 / (threads * target_regs);
+  int by_threads = 2048 / threads;
+  int b = by_smem < by_regs ? by_smem : by_regs;
+  b = b < by_threads ? b : by_threads;
+  return b < 1 ? 1 : b;
+}
+
+// =========================================== mass =====================================================
+template <typename T, int N1, int C>
+struct MassCol
+{
+  using G = ColGeom<T, N1, C>;
+  static constexpr int NE = G::viaC ? 3 : 2;
+  static constexpr int off_u = 0;
+  static constexpr int off_j = off_u + G::stage_bytes;
+  static constexpr int off_e = off_j + G::stage_bytes;
+  static constexpr int off_bar = off_e + NE * G::e_bytes;
+  static constexpr int smem_bytes = off_bar + 16;
+  static constexpr int min_blocks = min_blocks_for(G::NT, smem_bytes, sizeof(T) == 8 ? 64 : 48);
+};
+
+template <typename T, int N1, int C>
+__global__ void __launch_bounds__(ColGeom<T, N1, C>::NT, MassCol<T, N1, C>::min_blocks)
+mass_column_kernel(const __grid_constant__ TabA<T, N1> B, const T* __restrict__ U, T* __restrict__ W,
+                   const T* __restrict__ J, long long ntiles)
+{
+  using MC = MassCol<T, N1, C>;
+  using G = ColGeom<T, N1, C>;
+  using L = typename G::L;
+  using PA = typename G::PA;
+  using PB = typename G::PB;
+  using PC = typename G::PC;
+  using XBC = typename L::XBC;
+  using XAB = typename L::XAB;
+  using XCA = typename L::XCA;
+  constexpr int ND = G::ND, N2 = G::N2;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  T* uS = reinterpret_cast<T*>(smem + MC::off_u);
+  T* jS = reinterpret_cast<T*>(smem + MC::off_j);
+  T* E0 = reinterpret_cast<T*>(smem + MC::off_e);
+  T* E1 = reinterpret_cast<T*>(smem + MC::off_e + G::e_bytes);
+  T* E2 = reinterpret_cast<T*>(smem + MC::off_e + 2 * G::e_bytes); // only with viaC
+  const uint32_t barU = smem_u32(smem + MC::off_bar), barJ = barU + 8;
+
+  const int tid = threadIdx.x;
+  const int te = min(tid, G::ACTIVE - 1); // idle lanes clone the last active thread
+  const int c = te / N2, p = te - c * N2;
+  const int hi = p / N1, lo = p - hi * N1;
+
+  long long tile = blockIdx.x;
+  if (tid == 0)
+  {
+    mbar_init(barU, 1);
+    mbar_init(barJ, 1);
+    fence_mbar_init();
+    if (tile < ntiles)
+    {
+      mbar_expect_tx(barU, G::tile_bytes);
+      bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
+      mbar_expect_tx(barJ, G::tile_bytes);
+      bulk_g2s(smem_u32(jS), J + (size_t)tile * C * ND, G::tile_bytes, barJ);
+    }
+  }
+  __syncthreads();
+
+  uint32_t phase = 0;
+  for (; tile < ntiles; tile += gridDim.x, phase ^= 1)
+  {
+    const long long tn = tile + gridDim.x;
+    T x[N1];
+    // ---- phase C: forward along axis 0 (mass.hpp:36) -------------------------------------------------
+    mbar_wait(barU, phase);
+    if constexpr (G::viaC)
+    {
+      T d[N1];
+      mbar_wait(barJ, phase);
+      col_load<Nat<N1>, PC>(jS, c * ND + p, d);
+      col_store<XCA, PC>(E2, col_base<XCA, PC>(c, hi, lo), d);
+    }
+    contract_in(B.a, uS, c * ND + p, N2, x);
+    col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), x);
+    __syncthreads(); // (1) staging consumed, E0 complete
+    if (tid == 0 && tn < ntiles)
+    {
+      mbar_expect_tx(barU, G::tile_bytes);
+      bulk_g2s(smem_u32(uS), U + (size_t)tn * C * ND, G::tile_bytes, barU);
+      if constexpr (G::viaC)
+      {
+        mbar_expect_tx(barJ, G::tile_bytes);
+        bulk_g2s(smem_u32(jS), J + (size_t)tn * C * ND, G::tile_bytes, barJ);
+      }
+    }
+    // ---- phase B: axis 1 (mass.hpp:37) ------------------------------------------------------------------
+    contract_in(B.a, E0, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), x);
+    col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), x);
+    __syncthreads(); // (2)
+    // ---- phase A: axis 2, quadrature scaling (mass.hpp:38-41), back along axis 2 (mass.hpp:45, same matrix) --
+    contract_in(B.a, E1, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>(), x);
+    {
+      T d[N1];
+      if constexpr (G::viaC)
+        col_load<XCA, PA>(E2, col_base<XCA, PA>(c, hi, lo), d);
+      else
+      {
+        mbar_wait(barJ, phase);
+        col_load<Nat<N1>, PA>(jS, col_base<Nat<N1>, PA>(c, hi, lo), d);
+      }
+#pragma unroll
+      for (int r = 0; r < N1; ++r)
+        x[r] = x[r] * d[r];
+    }
+    contract_out(B.a, x, E0, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>());
+    __syncthreads(); // (3)
+    if constexpr (!G::viaC)
+    {
+      if (tid == 0 && tn < ntiles)
+      {
+        mbar_expect_tx(barJ, G::tile_bytes);
+        bulk_g2s(smem_u32(jS), J + (size_t)tn * C * ND, G::tile_bytes, barJ);
+      }
+    }
+    // ---- phase B': back along axis 1 (mass.hpp:46) ---------------------------------------------------
+    contract_in(B.a, E0, col_base<XAB, PB>(c, hi, lo), xstride<XAB, 1>(), x);
+    col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), x);
+    __syncthreads(); // (4)
+    // ---- phase C': back along axis 0 (mass.hpp:47), coalesced store of W ---------------------------------
+    contract_in(B.a, E1, col_base<XBC, PC>(c, hi, lo), xstride<XBC, 0>(), x);
+    if (tid < G::ACTIVE)
+    {
+      T* w = W + (size_t)tile * C * ND + c * ND + p;
+#pragma unroll
+      for (int r = 0; r < N1; ++r)
+        w[r * N2] = x[r];
+    }
+  }
+}
+
+// ========================================= stiffness ==================================================
+// Warp-private geometry ring.  For plane i0 the 6-value records of a warp's lanes (thread order =
+// point order) form `pieces` contiguous runs in HBM, one per cell the warp touches.  Piece k is
+// issued by lane k.  fp32 records are 24 bytes, so a piece may start / end on an 8-byte boundary:
+// the copy then covers the enclosing 16-byte units and readers skip the leading 8 bytes (`shift`);
+// tiles are whole 16-byte units, so the over-read never leaves the tile's own records.
+template <typename T, int N1, int C, int MODE, int NG>
+struct StiffCol
+{
+  using G = ColGeom<T, N1, C>;
+  static constexpr bool FULL = MODE == FEMTC_STIFFNESS_FULL;
+  static constexpr int RB = 6 * (int)sizeof(T);                          // record bytes
+  static constexpr int MAXP = (32 + G::N2 - 2) / G::N2 + 1;              // pieces a warp can have
+  static constexpr bool F32 = sizeof(T) == 4;
+  static constexpr int slot_bytes = up16(32 * RB) + (F32 ? 32 * MAXP + 16 : 0);
+  static constexpr int NE = G::viaC ? 4 : 3;
+  static constexpr int off_u = 0;
+  static constexpr int off_e = off_u + G::stage_bytes;
+  static constexpr int off_g = off_e + NE * G::e_bytes;
+  static constexpr int off_bar = off_g + G::NWARPS * NG * slot_bytes;
+  static constexpr int smem_bytes = off_bar + 8 * (1 + G::NWARPS * NG) + 8;
+  static constexpr int min_blocks = min_blocks_for(G::NT, smem_bytes, sizeof(T) == 8 ? (FULL ? 128 : 104) : (FULL ? 104 : 72));
+};
+
+template <typename T, int N1, int C, int MODE, int NG>
+__global__ void __launch_bounds__(ColGeom<T, N1, C>::NT, StiffCol<T, N1, C, MODE, NG>::min_blocks)
+stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restrict__ U, T* __restrict__ W,
+                        const T* __restrict__ Gm, long long ntiles)
+{
+  using SC = StiffCol<T, N1, C, MODE, NG>;
+  using G = ColGeom<T, N1, C>;
+  using L = typename G::L;
+  using PA = typename G::PA;
+  using PB = typename G::PB;
+  using PC = typename G::PC;
+  using XBC = typename L::XBC;
+  using XAB = typename L::XAB;
+  using XCA = typename L::XCA;
+  constexpr bool FULL = SC::FULL;
+  constexpr int ND = G::ND, N2 = G::N2, RB = SC::RB;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  T* uS = reinterpret_cast<T*>(smem + SC::off_u);
+  T* E0 = reinterpret_cast<T*>(smem + SC::off_e);
+  T* E1 = reinterpret_cast<T*>(smem + SC::off_e + G::e_bytes);
+  T* E2 = reinterpret_cast<T*>(smem + SC::off_e + 2 * G::e_bytes);
+  T* E3 = reinterpret_cast<T*>(smem + SC::off_e + 3 * G::e_bytes); // only with viaC
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  unsigned char* gRing = smem + SC::off_g + warp * NG * SC::slot_bytes;
+  const uint32_t barU = smem_u32(smem + SC::off_bar);
+  const uint32_t barG = barU + 8 + warp * NG * 8;
+
+  const int te = min(tid, G::ACTIVE - 1);
+  const int c = te / N2, p = te - c * N2;
+  const int hi = p / N1, lo = p - hi * N1;
+
+  // ---- this warp's geometry pieces (tile independent) -------------------------------------------------
+  const int q0 = warp * 32;                                  // first thread of the warp
+  const int nAct = min(32, G::ACTIVE - q0);                  // active lanes of the warp
+  const int cFirst = q0 / N2;
+  const int npieces = (q0 + nAct - 1) / N2 - cFirst + 1;
+  // as issuer of piece `lane`
+  int is_cell = cFirst + lane;
+  int is_qs = max(q0, is_cell * N2), is_qe = min(q0 + nAct, (is_cell + 1) * N2);
+  const bool issuer = lane < npieces;
+  const int is_rec = is_cell * ND + (is_qs - is_cell * N2);  // record index inside the tile, plane 0
+  const int is_cnt = is_qe - is_qs;
+  const int is_dst = up16(RB * (is_qs - q0)) + (SC::F32 ? 32 * lane : 0);
+  // as reader: my piece is the one of my (cloned) thread
+  const int my_k = c - cFirst;
+  const int my_qs = max(q0, c * N2);
+  const int my_par = (c * ND + (my_qs - c * N2)) & 1;         // fp32: parity of the piece's first record
+  const int my_off = up16(RB * (my_qs - q0)) + (SC::F32 ? 32 * my_k : 0) + RB * (te - my_qs);
+
+  const long long my_tiles = (long long)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long q_end = my_tiles * N1;
+
+  auto load_plane = [&](long long q, int slot)
+  {
+    if (issuer)
+    {
+      const long long t = blockIdx.x + (q / N1) * (long long)gridDim.x;
+      const int plane = (int)(q % N1);
+      const int rec = is_rec + plane * N2;
+      const int sh = SC::F32 ? (rec & 1) : 0;                 // tile bases are even record counts
+      const uint32_t bytes = (uint32_t)up16(RB * is_cnt + 8 * sh);
+      const unsigned char* src = reinterpret_cast<const unsigned char*>(Gm) +
+                                 ((size_t)t * C * ND + rec) * RB - 8 * sh;
+      mbar_expect_tx(barG + 8 * slot, bytes);
+      bulk_g2s(smem_u32(gRing + slot * SC::slot_bytes + is_dst), src, bytes, barG + 8 * slot);
+    }
+  };
+
+  long long tile = blockIdx.x;
+  if (tid == 0)
+  {
+    mbar_init(barU, 1);
+    fence_mbar_init();
+  }
+  if (lane == 0)
+  {
+    for (int s = 0; s < NG; ++s)
+      mbar_init(barG + 8 * s, npieces);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0 && tile < ntiles)
+  {
+    mbar_expect_tx(barU, G::tile_bytes);
+    bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
+  }
+  long long q_issue = 0, q = 0;
+  for (; q_issue < NG && q_issue < q_end; ++q_issue)
+    load_plane(q_issue, (int)(q_issue % NG));
+
+  uint32_t phase = 0;
+  for (; tile < ntiles; tile += gridDim.x, phase ^= 1)
+  {
+    const long long tn = tile + gridDim.x;
+    auto next_u = [&]()
+    {
+      if (tid == 0 && tn < ntiles)
+      {
+        mbar_expect_tx(barU, G::tile_bytes);
+        bulk_g2s(smem_u32(uS), U + (size_t)tn * C * ND, G::tile_bytes, barU);
+      }
+    };
+    // ---- phase A: u columns along axis 2; t = A2 u (FULL: s = D2 u) ------------------------------------
+    {
+      T y[N1], z[N1];
+      mbar_wait(barU, phase);
+      const T* src = uS;
+      int sbase = col_base<Nat<N1>, PA>(c, hi, lo), sstride = 1;
+      if constexpr (G::viaC)
+      {
+        col_load<Nat<N1>, PC>(uS, c * ND + p, y);
+        col_store<XCA, PC>(E3, col_base<XCA, PC>(c, hi, lo), y);
+        __syncthreads(); // (0)
+        next_u();
+        src = E3, sbase = col_base<XCA, PA>(c, hi, lo), sstride = xstride<XCA, 2>();
+      }
+      if constexpr (!FULL)
+        contract_in(B.a, src, sbase, sstride, y);
+      else
+      {
+        contract_in2(B.a, B.d, src, sbase, sstride, y, z);
+        col_store<XAB, PA>(E1, col_base<XAB, PA>(c, hi, lo), z);
+      }
+      col_store<XAB, PA>(E0, col_base<XAB, PA>(c, hi, lo), y);
+    }
+    if constexpr (!G::viaC)
+      if (tid == 0)
+        bulk_wait_read0(); // the previous tile's W store has finished reading E2
+    __syncthreads(); // (1)
+    if constexpr (!G::viaC)
+      next_u();
+    // ---- phase B: axis 1 ------------------------------------------------------------------------------------
+    {
+      T ya[N1], yd[N1];
+      contract_in2(B.a, B.d, E0, col_base<XAB, PB>(c, hi, lo), xstride<XAB, 1>(), ya, yd); // A1 A2 u, D1 A2 u
+      if constexpr (!FULL)
+      {
+        col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), ya);
+        col_store<XBC, PB>(E2, col_base<XBC, PB>(c, hi, lo), yd);
+      }
+      else
+      {
+        T ys[N1];
+        contract_in(B.a, E1, col_base<XAB, PB>(c, hi, lo), xstride<XAB, 1>(), ys);           // A1 D2 u
+        __syncthreads(); // (1b) E0, E1 are rewritten below
+        col_store<XBC, PB>(E0, col_base<XBC, PB>(c, hi, lo), ya);
+        col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), yd);
+        col_store<XBC, PB>(E2, col_base<XBC, PB>(c, hi, lo), ys);
+      }
+    }
+    __syncthreads(); // (2)
+    // ---- phase C: axis 0 forward, geometry, axis 0 backward -- fused plane by plane ---------------------------
+    // For plane i0:  w0 = D(i0,:) ta, w1 = A(i0,:) td, w2 = A(i0,:) ta   [REF_EXACT: stiffness.hpp:68-77]
+    //                                                  w2 = A(i0,:) sa   [FULL]
+    // then the 3x3 symmetric geometry map (stiffness.hpp:14-29) and h(:) += M(:,i0) f.
+    {
+      T ta[N1], td[N1], h2[N1];
+      T sa[FULL ? N1 : 1], h0[FULL ? N1 : 1], h1[FULL ? N1 : 1];
+      if constexpr (!FULL)
+      {
+        col_load<XBC, PC>(E1, col_base<XBC, PC>(c, hi, lo), ta);
+        col_load<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), td);
+      }
+      else
+      {
+        col_load<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), ta);
+        col_load<XBC, PC>(E1, col_base<XBC, PC>(c, hi, lo), td);
+        col_load<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), sa);
+      }
+#pragma unroll
+      for (int i = 0; i < N1; ++i)
+      {
+        h2[i] = T(0);
+        if constexpr (FULL)
+          h0[i] = h1[i] = T(0);
+      }
+#pragma unroll(Roll<T>::in)
+      for (int i0 = 0; i0 < N1; ++i0, ++q)
+      {
+        const T w0 = row_dot(B.d, i0, ta);
+        const T w1 = row_dot(B.a, i0, td);
+        T w2;
+        if constexpr (FULL)
+          w2 = row_dot(B.a, i0, sa);
+        else
+          w2 = row_dot(B.a, i0, ta);
+        const int slot = (int)(q % NG);
+        mbar_wait(barG + 8 * slot, (uint32_t)((q / NG) & 1));
+        const int sh = SC::F32 ? ((my_par + i0 * (N2 & 1)) & 1) : 0;
+        const T* gp = reinterpret_cast<const T*>(gRing + slot * SC::slot_bytes + my_off + 8 * sh);
+        T g[6];
+        if constexpr (sizeof(T) == 8)
+        {
+          const double2 a = *reinterpret_cast<const double2*>(gp);
+          g[0] = a.x, g[1] = a.y;
+          if constexpr (FULL)
+          {
+            const double2 b = *reinterpret_cast<const double2*>(gp + 2);
+            const double2 cc = *reinterpret_cast<const double2*>(gp + 4);
+            g[2] = b.x, g[3] = b.y, g[4] = cc.x, g[5] = cc.y;
+          }
+          else
+            g[2] = gp[2];
+        }
+        else
+        {
+          const float2 a = *reinterpret_cast<const float2*>(gp);
+          g[0] = a.x, g[1] = a.y;
+          if constexpr (FULL)
+          {
+            const float2 b = *reinterpret_cast<const float2*>(gp + 2);
+            const float2 cc = *reinterpret_cast<const float2*>(gp + 4);
+            g[2] = b.x, g[3] = b.y, g[4] = cc.x, g[5] = cc.y;
+          }
+          else
+            g[2] = gp[2];
+        }
+        const T f2 = fma_t(g[0], w2, fma_t(g[1], w1, g[2] * w0));
+        if constexpr (FULL)
+        {
+          const T f0 = fma_t(g[2], w2, fma_t(g[4], w1, g[5] * w0));
+          const T f1 = fma_t(g[1], w2, fma_t(g[3], w1, g[4] * w0));
+          col_axpy(B.d, i0, f0, h0);                            // D0 f0
+          col_axpy(B.a, i0, f1, h1);                            // A0 f1
+        }
+        // REF_EXACT: only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
+        col_axpy(B.a, i0, f2, h2);                              // A0 f2
+        __syncwarp(); // every lane is done with this slot: request the chunk NG ahead into it
+        if (q_issue < q_end)
+        {
+          load_plane(q_issue, slot);
+          ++q_issue;
+        }
+      }
+      if constexpr (!FULL)
+        col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h2);
+      else
+      {
+        __syncthreads(); // (2b) E0..E2 were read by this phase
+        col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h0);
+        col_store<XBC, PC>(E1, col_base<XBC, PC>(c, hi, lo), h1);
+        col_store<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), h2);
+      }
+    }
+    __syncthreads(); // (3)
+    // ---- phase B': back along axis 1 --------------------------------------------------------------------------
+    {
+      T m[N1];
+      contract_in(B.a, E0, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), m);              // A1 (.)
+      if constexpr (!FULL)
+        col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), m);
+      else
+      {
+        T n[N1];
+        contract_in_add(B.d, E1, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), m);        // + D1 A0 f1
+        contract_in(B.a, E2, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), n);            // A1 A0 f2
+        __syncthreads(); // (3b)
+        col_store<XAB, PB>(E0, col_base<XAB, PB>(c, hi, lo), m);
+        col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), n);
+      }
+    }
+    __syncthreads(); // (4)
+    // ---- phase A': back along axis 2, W ---------------------------------------------------------------------------
+    {
+      T out[N1];
+      if constexpr (!FULL)
+        contract_in(B.d, E1, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>(), out);          // D2 (.)
+      else
+      {
+        contract_in(B.a, E0, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>(), out);
+        contract_in_add(B.d, E1, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>(), out);
+      }
+      if constexpr (G::viaC)
+      {
+        col_store<XCA, PA>(E2, col_base<XCA, PA>(c, hi, lo), out);
+        __syncthreads(); // (5)
+        col_load<XCA, PC>(E2, col_base<XCA, PC>(c, hi, lo), out);
+        if (tid < G::ACTIVE)
+        {
+          T* w = W + (size_t)tile * C * ND + c * ND + p;
+#pragma unroll
+          for (int r = 0; r < N1; ++r)
+            w[r * N2] = out[r];
+        }
+      }
+      else
+      {
+        col_store<Nat<N1>, PA>(E2, col_base<Nat<N1>, PA>(c, hi, lo), out);
+        fence_proxy_async();
+        __syncthreads(); // (5)
+        if (tid == 0)
+        {
+          bulk_s2g(W + (size_t)tile * C * ND, smem_u32(E2), G::tile_bytes);
+          bulk_commit();
+        }
+      }
+    }
+  }
+  if constexpr (!G::viaC)
+    if (tid == 0)
+      bulk_wait_read0();
+}
+
+// ---- launch helpers --------------------------------------------------------------------------------------
+inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename K>
+int plan_blocks(K kernel, int threads, size_t smem, int& blocks_per_sm)
+{
+  int dev = 0, max_optin = 0;
+  FEMTC_CUDA(cudaGetDevice(&dev));
+  FEMTC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  if ((size_t)max_optin < smem)
+  {
+    set_error("column kernel does not fit on an SM");
+    return FEMTC_ERR_CUDA;
+  }
+  FEMTC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FEMTC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+  FEMTC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, threads, smem));
+  if (blocks_per_sm < 1)
+  {
+    set_error("column kernel does not fit on an SM");
+    return FEMTC_ERR_CUDA;
+  }
+  return FEMTC_OK;
+}
+
+template <typename T, int N1, int C>
+long long run_mass_col(const MassArgs<T>& a)
+{
+  using MC = MassCol<T, N1, C>;
+  using G = ColGeom<T, N1, C>;
+  const long long ntiles = (long long)(a.num_cells / C);
+  if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.detJ))
+    return 0;
+  TabA<T, N1> B;
+  for (int i = 0; i < N1 * N1; ++i)
+    B.a[i] = a.phi_host[i];
+  auto kernel = mass_column_kernel<T, N1, C>;
+  int bps = 0;
+  int rc = plan_blocks(kernel, G::NT, MC::smem_bytes, bps);
+  if (rc)
+    return -rc;
+  const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
+  kernel<<<grid, G::NT, MC::smem_bytes, a.stream>>>(B, a.U, a.W, a.detJ, ntiles);
+  count_launch();
+  if (cudaGetLastError() != cudaSuccess)
+    return -FEMTC_ERR_CUDA;
+  return ntiles * C;
+}
+
+template <typename T, int N1, int C, int MODE, int NG>
+long long run_stiff_col(const StiffnessArgs<T>& a)
+{
+  using SC = StiffCol<T, N1, C, MODE, NG>;
+  using G = ColGeom<T, N1, C>;
+  const long long ntiles = (long long)(a.num_cells / C);
+  if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.G))
+    return 0;
+  TabAD<T, N1> B;
+  for (int i = 0; i < N1 * N1; ++i)
+  {
+    B.a[i] = a.A_host[i];
+    B.d[i] = a.D_host[i];
+  }
+  auto kernel = stiffness_column_kernel<T, N1, C, MODE, NG>;
+  int bps = 0;
+  int rc = plan_blocks(kernel, G::NT, SC::smem_bytes, bps);
+  if (rc)
+    return -rc;
+  const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
+  kernel<<<grid, G::NT, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
+  count_launch();
+  if (cudaGetLastError() != cudaSuccess)
+    return -FEMTC_ERR_CUDA;
+  return ntiles * C;
+}
+
+template <typename T, int N1, int C, int NG>
+long long run_stiff_col_mode(const StiffnessArgs<T>& a)
+{
+  return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG>(a)
+                                        : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG>(a);
+}
+
+} // namespace
+
+// Which (type, n1) the column family serves: everything the slab kernels do not.
+template <typename T>
+long long launch_mass_column(const MassArgs<T>& a)
+{
+  const int n1 = a.degree + 1;
+  switch (n1)
+  {
+  case 6: return run_mass_col<T, 6, default_cells<T, 6>()>(a);
+  case 7: return run_mass_col<T, 7, default_cells<T, 7>()>(a);
+  case 8: return run_mass_col<T, 8, default_cells<T, 8>()>(a);
+  case 9: return run_mass_col<T, 9, default_cells<T, 9>()>(a);
+  default: break;
+  }
+  if constexpr (sizeof(T) == 4)
+  {
+    if (n1 == 3) return run_mass_col<T, 3, default_cells<T, 3>()>(a);
+    if (n1 == 5) return run_mass_col<T, 5, default_cells<T, 5>()>(a);
+  }
+  return 0;
+}
+
+template <typename T>
+long long launch_stiffness_column(const StiffnessArgs<T>& a)
+{
+  const int n1 = a.degree + 1;
+  switch (n1)
+  {
+  case 2: return run_stiff_col_mode<T, 2, default_cells<T, 2>(), 2>(a);
+  case 6: return run_stiff_col_mode<T, 6, default_cells<T, 6>(), 2>(a);
+  case 7: return run_stiff_col_mode<T, 7, default_cells<T, 7>(), 2>(a);
+  case 8: return run_stiff_col_mode<T, 8, default_cells<T, 8>(), 2>(a);
+  case 9: return run_stiff_col_mode<T, 9, default_cells<T, 9>(), 2>(a);
+  default: break;
+  }
+  if constexpr (sizeof(T) == 4)
+  {
+    if (n1 == 3) return run_stiff_col_mode<T, 3, default_cells<T, 3>(), 2>(a);
+    if (n1 == 5) return run_stiff_col_mode<T, 5, default_cells<T, 5>(), 2>(a);
+  }
+  return 0;
+}
+
+template long long launch_mass_column<double>(const MassArgs<double>&);
+template long long launch_mass_column<float>(const MassArgs<float>&);
+template long long launch_stiffness_column<double>(const StiffnessArgs<double>&);
+template long long launch_stiffness_column<float>(const StiffnessArgs<float>&);
+
+} // namespace femtc

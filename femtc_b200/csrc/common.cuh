@@ -79,6 +79,12 @@ template <typename T>
 long long launch_mass_tiled(const MassArgs<T>& a);
 template <typename T>
 long long launch_stiffness_tiled(const StiffnessArgs<T>& a);
+// column_kernels.cu -- n1^2 threads per cell, degrees 5..8 and the shapes the slab kernels skip;
+// same return convention as the tiled launchers
+template <typename T>
+long long launch_mass_column(const MassArgs<T>& a);
+template <typename T>
+long long launch_stiffness_column(const StiffnessArgs<T>& a);
 int tiled_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8]);
 
 int sm_count();
