@@ -42,17 +42,41 @@ constexpr int cmaxi(int a, int b) { return a > b ? a : b; }
 constexpr int up16(int bytes) { return (bytes + 15) & ~15; }
 constexpr int up128(int bytes) { return (bytes + 127) & ~127; }
 
-template <typename T, int N1>
-struct TabA
+// The 1-D tables as kernel parameters.  Column-major like the reference (A(i,p) = a[i + p*LD]) but
+// with the leading dimension padded to an even count, plus the transposes (at[p + i*LD] = A(i,p)),
+// so that both a column and a row of a matrix are contiguous 16-byte-aligned runs: fp64 entries
+// then reach the uniform registers two per LDCU.128.
+template <int N1>
+constexpr int tab_ld()
 {
-  T a[N1 * N1];
+  return (N1 + 1) & ~1;
+}
+template <typename T, int N1>
+struct alignas(16) TabA
+{
+  static constexpr int LD = tab_ld<N1>();
+  T a[N1 * LD];
+  T at[N1 * LD];
 };
 template <typename T, int N1>
-struct TabAD
+struct alignas(16) TabAD
 {
-  T a[N1 * N1];
-  T d[N1 * N1];
+  static constexpr int LD = tab_ld<N1>();
+  T a[N1 * LD];
+  T d[N1 * LD];
+  T at[N1 * LD];
+  T dt[N1 * LD];
 };
+template <typename T, int N1>
+void fill_table(T* dst, const T* src_colmajor, bool transpose)
+{
+  constexpr int LD = tab_ld<N1>();
+  for (int i = 0; i < N1 * LD; ++i)
+    dst[i] = T(0);
+  for (int i = 0; i < N1; ++i)
+    for (int p = 0; p < N1; ++p)
+      (transpose ? dst[p + i * LD] : dst[i + p * LD]) = src_colmajor[i + p * N1];
+}
 
 // ---- contractions -------------------------------------------------------------------------------------
 // One side of every contraction is shared memory (the column being read, or the column being
@@ -63,92 +87,176 @@ struct TabAD
 // unrolled kernel makes ptxas hoist whole matrices into (spilled) registers -- the rolled form keeps
 // the working set to one matrix row / column.  Sums run over p ascending, starting from zero
 // (0 + a*b is exact, so this equals the reference's "Ctemp = 0; Ctemp += a*b": linalg.hpp:57,128).
-template <typename T>
+template <typename T, int N1>
 struct Roll
 {
-  static constexpr int in = sizeof(T) == 8 ? 1 : 16;  // unroll factor of the shared-memory-side loop
+  // matrix columns / rows handled per trip of a rolled loop: fp64 keeps at most ~27 entries
+  // (54 uniform registers) in flight; fp32 (and tiny n1) is fully unrolled
+  static constexpr int in = (sizeof(T) == 4 || N1 <= 4) ? N1 : (N1 % 3 == 0 ? 3 : 2);
+  static constexpr int plane = (sizeof(T) == 4 || N1 <= 4) ? N1 : 1;
 };
 
-// y[i] = sum_p M[i + p*N1] * buf[base + p*stride]            (shared memory -> registers)
+// N1 consecutive table entries starting at the even offset `off` (a 16-byte boundary): fp64 pairs
+// are fetched as one 128-bit constant load
 template <typename T, int N1>
-__device__ __forceinline__ void contract_in(const T (&M)[N1 * N1], const T* buf, int base, int stride, T (&y)[N1])
+__device__ __forceinline__ void tab_run(const T* M, int off, T (&m)[N1])
+{
+  if constexpr (sizeof(T) == 8)
+  {
+#pragma unroll
+    for (int i = 0; i < N1; i += 2)
+    {
+      const double2 v = *reinterpret_cast<const double2*>(M + off + i);
+      m[i] = v.x;
+      if (i + 1 < N1)
+        m[i + 1] = v.y;
+    }
+  }
+  else
+  {
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      m[i] = M[off + i];
+  }
+}
+
+// One trip: columns p0 .. p0+CNT-1 of the tables (table offset `off` = p0*LD) applied to the values
+// at ptr[0], ptr[stride], ...
+template <int CNT, bool DUAL, typename T, int N1>
+__device__ __forceinline__ void contract_in_trip(const T* Ma, const T* Mb, int off, const T* ptr, int stride,
+                                                 T (&ya)[N1], T (&yb)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  T xp[CNT];
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+    xp[u] = ptr[u * stride];
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+  {
+    T m[N1];
+    tab_run<T, N1>(Ma, off + u * LD, m);
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      ya[i] = fma_t(m[i], xp[u], ya[i]);
+    if constexpr (DUAL)
+    {
+      tab_run<T, N1>(Mb, off + u * LD, m);
+#pragma unroll
+      for (int i = 0; i < N1; ++i)
+        yb[i] = fma_t(m[i], xp[u], yb[i]);
+    }
+  }
+}
+template <bool DUAL, typename T, int N1>
+__device__ __forceinline__ void contract_in_loop(const T* Ma, const T* Mb, const T* ptr, int stride, T (&ya)[N1],
+                                                 T (&yb)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  constexpr int U = Roll<T, N1>::in;
+  constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
+  if constexpr (TRIPS == 1)
+    contract_in_trip<U, DUAL>(Ma, Mb, 0, ptr, stride, ya, yb);
+  else
+  {
+    // the table offset is a separate, uniform induction variable; the shared-memory address is a
+    // pointer increment -- so the matrix fetches stay on the uniform datapath (LDCU)
+    int off = 0;
+#pragma unroll 1
+    for (int t = 0; t < TRIPS; ++t)
+    {
+      contract_in_trip<U, DUAL>(Ma, Mb, off, ptr, stride, ya, yb);
+      ptr += U * stride;
+      off += U * LD;
+    }
+  }
+  if constexpr (REM > 0 && TRIPS != 1)
+    contract_in_trip<REM, DUAL>(Ma, Mb, TRIPS * U * LD, ptr, stride, ya, yb);
+}
+
+// y[i] = sum_p A(i,p) * buf[base + p*stride]                  (shared memory -> registers)
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in(const T (&M)[N1 * tab_ld<N1>()], const T* buf, int base, int stride, T (&y)[N1])
 {
 #pragma unroll
   for (int i = 0; i < N1; ++i)
     y[i] = T(0);
-#pragma unroll(Roll<T>::in)
-  for (int p = 0; p < N1; ++p)
-  {
-    const T xp = buf[base + p * stride];
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-      y[i] = fma_t(M[i + p * N1], xp, y[i]);
-  }
+  contract_in_loop<false>(M, M, buf + base, stride, y, y);
 }
-// y[i] += sum_p M[i + p*N1] * buf[base + p*stride]
+// y[i] += sum_p A(i,p) * buf[base + p*stride]
 template <typename T, int N1>
-__device__ __forceinline__ void contract_in_add(const T (&M)[N1 * N1], const T* buf, int base, int stride, T (&y)[N1])
+__device__ __forceinline__ void contract_in_add(const T (&M)[N1 * tab_ld<N1>()], const T* buf, int base, int stride, T (&y)[N1])
 {
-#pragma unroll(Roll<T>::in)
-  for (int p = 0; p < N1; ++p)
-  {
-    const T xp = buf[base + p * stride];
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-      y[i] = fma_t(M[i + p * N1], xp, y[i]);
-  }
+  contract_in_loop<false>(M, M, buf + base, stride, y, y);
 }
 // two matrices applied to the same column
 template <typename T, int N1>
-__device__ __forceinline__ void contract_in2(const T (&Ma)[N1 * N1], const T (&Mb)[N1 * N1], const T* buf, int base,
+__device__ __forceinline__ void contract_in2(const T (&Ma)[N1 * tab_ld<N1>()], const T (&Mb)[N1 * tab_ld<N1>()], const T* buf, int base,
                                              int stride, T (&ya)[N1], T (&yb)[N1])
 {
 #pragma unroll
   for (int i = 0; i < N1; ++i)
     ya[i] = yb[i] = T(0);
-#pragma unroll(Roll<T>::in)
-  for (int p = 0; p < N1; ++p)
-  {
-    const T xp = buf[base + p * stride];
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-    {
-      ya[i] = fma_t(Ma[i + p * N1], xp, ya[i]);
-      yb[i] = fma_t(Mb[i + p * N1], xp, yb[i]);
-    }
-  }
+  contract_in_loop<true>(Ma, Mb, buf + base, stride, ya, yb);
 }
-// buf[base + i*stride] = sum_p M[i + p*N1] * z[p]             (registers -> shared memory)
+// row `i` of A times a register column: sum_p A(i,p) * z[p]      (MT = transposed table; off = i*LD)
 template <typename T, int N1>
-__device__ __forceinline__ void contract_out(const T (&M)[N1 * N1], const T (&z)[N1], T* buf, int base, int stride)
+__device__ __forceinline__ T row_dot_off(const T* MT, int off, const T (&z)[N1])
 {
-#pragma unroll(Roll<T>::in)
-  for (int i = 0; i < N1; ++i)
-  {
-    T acc = M[i] * z[0];
-#pragma unroll
-    for (int p = 1; p < N1; ++p)
-      acc = fma_t(M[i + p * N1], z[p], acc);
-    buf[base + i * stride] = acc;
-  }
-}
-// row `i` of M times a register column: sum_p M[i + p*N1] * z[p]   (i may be dynamic)
-template <typename T, int N1>
-__device__ __forceinline__ T row_dot(const T (&M)[N1 * N1], int i, const T (&z)[N1])
-{
-  T acc = M[i] * z[0];
+  T m[N1];
+  tab_run<T, N1>(MT, off, m);
+  T acc = m[0] * z[0];
 #pragma unroll
   for (int p = 1; p < N1; ++p)
-    acc = fma_t(M[i + p * N1], z[p], acc);
+    acc = fma_t(m[p], z[p], acc);
   return acc;
 }
-// y[i] += M[i + p*N1] * f for all i                              (p may be dynamic)
 template <typename T, int N1>
-__device__ __forceinline__ void col_axpy(const T (&M)[N1 * N1], int p, T f, T (&y)[N1])
+__device__ __forceinline__ T row_dot(const T (&MT)[N1 * tab_ld<N1>()], int i, const T (&z)[N1])
 {
+  return row_dot_off<T, N1>(MT, i * tab_ld<N1>(), z);
+}
+// buf[base + i*stride] = sum_p A(i,p) * z[p]                   (registers -> shared memory)
+// MT is the transposed table, MT[p + i*LD] = A(i,p): row i is a contiguous run.
+template <typename T, int N1>
+__device__ __forceinline__ void contract_out(const T (&MT)[N1 * tab_ld<N1>()], const T (&z)[N1], T* buf, int base, int stride)
+{
+  constexpr int LD = tab_ld<N1>();
+  constexpr int U = Roll<T, N1>::in;
+  constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
+  T* ptr = buf + base;
+  if constexpr (TRIPS == 1)
+  {
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      ptr[i * stride] = row_dot_off<T, N1>(MT, i * LD, z);
+  }
+  else
+  {
+    int off = 0;
+#pragma unroll 1
+    for (int t = 0; t < TRIPS; ++t)
+    {
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        ptr[u * stride] = row_dot_off<T, N1>(MT, off + u * LD, z);
+      ptr += U * stride;
+      off += U * LD;
+    }
+#pragma unroll
+    for (int u = 0; u < REM; ++u)
+      ptr[u * stride] = row_dot_off<T, N1>(MT, (TRIPS * U + u) * LD, z);
+  }
+}
+// y[i] += A(i,p) * f for all i                                   (off = p*LD, may be dynamic)
+template <typename T, int N1>
+__device__ __forceinline__ void col_axpy(const T (&M)[N1 * tab_ld<N1>()], int p, T f, T (&y)[N1])
+{
+  T m[N1];
+  tab_run<T, N1>(M, p * tab_ld<N1>(), m);
 #pragma unroll
   for (int i = 0; i < N1; ++i)
-    y[i] = fma_t(M[i + p * N1], f, y[i]);
+    y[i] = fma_t(m[i], f, y[i]);
 }
 
 template <class X, int AXIS>
@@ -342,7 +450,7 @@ mass_column_kernel(const __grid_constant__ TabA<T, N1> B, const T* __restrict__ 
       for (int r = 0; r < N1; ++r)
         x[r] = x[r] * d[r];
     }
-    contract_out(B.a, x, E0, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>());
+    contract_out(B.at, x, E0, col_base<XAB, PA>(c, hi, lo), xstride<XAB, 2>());
     __syncthreads(); // (3)
     if constexpr (!G::viaC)
     {
@@ -569,16 +677,16 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         if constexpr (FULL)
           h0[i] = h1[i] = T(0);
       }
-#pragma unroll(Roll<T>::in)
+#pragma unroll(Roll<T, N1>::in)
       for (int i0 = 0; i0 < N1; ++i0, ++q)
       {
-        const T w0 = row_dot(B.d, i0, ta);
-        const T w1 = row_dot(B.a, i0, td);
+        const T w0 = row_dot(B.dt, i0, ta);
+        const T w1 = row_dot(B.at, i0, td);
         T w2;
         if constexpr (FULL)
-          w2 = row_dot(B.a, i0, sa);
+          w2 = row_dot(B.at, i0, sa);
         else
-          w2 = row_dot(B.a, i0, ta);
+          w2 = row_dot(B.at, i0, ta);
         const int slot = (int)(q % NG);
         mbar_wait(barG + 8 * slot, (uint32_t)((q / NG) & 1));
         const int sh = SC::F32 ? ((my_par + i0 * (N2 & 1)) & 1) : 0;
@@ -730,8 +838,8 @@ long long run_mass_col(const MassArgs<T>& a)
   if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.detJ))
     return 0;
   TabA<T, N1> B;
-  for (int i = 0; i < N1 * N1; ++i)
-    B.a[i] = a.phi_host[i];
+  fill_table<T, N1>(B.a, a.phi_host, false);
+  fill_table<T, N1>(B.at, a.phi_host, true);
   auto kernel = mass_column_kernel<T, N1, C>;
   int bps = 0;
   int rc = plan_blocks(kernel, G::NT, MC::smem_bytes, bps);
@@ -754,11 +862,10 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
   if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.G))
     return 0;
   TabAD<T, N1> B;
-  for (int i = 0; i < N1 * N1; ++i)
-  {
-    B.a[i] = a.A_host[i];
-    B.d[i] = a.D_host[i];
-  }
+  fill_table<T, N1>(B.a, a.A_host, false);
+  fill_table<T, N1>(B.d, a.D_host, false);
+  fill_table<T, N1>(B.at, a.A_host, true);
+  fill_table<T, N1>(B.dt, a.D_host, true);
   auto kernel = stiffness_column_kernel<T, N1, C, MODE, NG>;
   int bps = 0;
   int rc = plan_blocks(kernel, G::NT, SC::smem_bytes, bps);
