@@ -16,7 +16,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 OBJ = CSRC / "_obj"
 LIB = PKG / "libfemtc_b200.so"
-SOURCES = ["api.cu", "generic_kernels.cu", "tiled_kernels.cu", "column_kernels.cu"]
+SOURCES = ["api.cu", "generic_kernels.cu", "tiled_kernels.cu", "column_kernels.cu", "cell_kernels.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

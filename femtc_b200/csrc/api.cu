@@ -134,7 +134,9 @@ static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T
   const long long force = g_opt_kernel.load();
   if (force != 1 && degree <= 8)
   {
-    long long n = launch_mass_tiled<T>(a);
+    long long n = launch_mass_cell<T>(a);
+    if (n == 0)
+      n = launch_mass_tiled<T>(a);
     if (n == 0)
       n = launch_mass_column<T>(a);
     if (n < 0)
@@ -202,7 +204,9 @@ static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, co
   const long long force = g_opt_kernel.load();
   if (force != 1 && degree <= 8)
   {
-    long long n = launch_stiffness_tiled<T>(a);
+    long long n = launch_stiffness_cell<T>(a);
+    if (n == 0)
+      n = launch_stiffness_tiled<T>(a);
     if (n == 0)
       n = launch_stiffness_column<T>(a);
     if (n < 0)

@@ -85,6 +85,11 @@ template <typename T>
 long long launch_mass_column(const MassArgs<T>& a);
 template <typename T>
 long long launch_stiffness_column(const StiffnessArgs<T>& a);
+// cell_kernels.cu -- one thread per cell, n1 = 2 and (fp32) n1 = 3; same return convention
+template <typename T>
+long long launch_mass_cell(const MassArgs<T>& a);
+template <typename T>
+long long launch_stiffness_cell(const StiffnessArgs<T>& a);
 int tiled_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8]);
 
 int sm_count();

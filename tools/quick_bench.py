@@ -45,15 +45,26 @@ def main():
     ap.add_argument("--variants", default="0")
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--max-gb", type=float, default=60.0)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--configs", default="", help="explicit list op:dtype:P:mode[,...] instead of the cross product")
     a = ap.parse_args()
+    if a.configs:
+        for item in a.configs.split(","):
+            op, dt, P, mode = item.split(":")
+            sweep(a, [op], [dt], [int(P)], [int(mode)])
+    else:
+        sweep(a, a.ops.split(","), a.dtypes.split(","), parse_range(a.degrees), parse_range(a.modes))
+
+
+def sweep(a, ops, dtypes, degrees, modes):
     peak = peak_gbs()
     femtc.set_option("kernel", a.kernel)
     rng = np.random.default_rng(1)
-    for op in a.ops.split(","):
-        for dt in a.dtypes.split(","):
+    for op in ops:
+        for dt in dtypes:
             tdt = torch.float64 if dt == "f64" else torch.float32
             sz = 8 if dt == "f64" else 4
-            for P in parse_range(a.degrees):
+            for P in degrees:
                 nd = (P + 1) ** 3
                 gw = 6 if op == "stiffness" else 1
                 cells = a.cells
@@ -63,7 +74,7 @@ def main():
                 U = fill_uniform(torch.empty(cells * nd, dtype=tdt, device="cuda"), 1, 1)
                 G = fill_uniform(torch.empty(cells * nd * gw, dtype=tdt, device="cuda"), 1, 2)
                 W = torch.empty_like(U)
-                for mode in ([0] if op == "mass" else parse_range(a.modes)):
+                for mode in ([0] if op == "mass" else modes):
                     for variant in parse_range(a.variants):
                         femtc.set_option("variant", variant)
 
@@ -72,7 +83,7 @@ def main():
                                 femtc.mass_operator(phi, U, W, G, cells, P)
                             else:
                                 femtc.stiffness_operator(phi, U, W, G, cells, P, mode=mode)
-                        for _ in range(3):
+                        for _ in range(a.warmup):
                             run()
                         torch.cuda.synchronize()
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
