@@ -5,10 +5,12 @@ There is no fallback of any kind: if the shared library has not been built the i
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libfemtc_b200.so"
+# FEMTC_B200_LIB: another build of the same library (development A/B runs); never a fallback
+LIB_PATH = Path(os.environ.get("FEMTC_B200_LIB") or PKG / "libfemtc_b200.so")
 
 OK, ERR_DEGREE, ERR_ORDER, ERR_BLOCK, ERR_MODE, ERR_LENGTH, ERR_CUDA, ERR_ARG = range(8)
 STIFFNESS_REF_EXACT, STIFFNESS_FULL = 0, 1

@@ -14,8 +14,11 @@ from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
-OBJ = CSRC / "_obj"
-LIB = PKG / "libfemtc_b200.so"
+# development knobs: FEMTC_LIB_SUFFIX=_x FEMTC_EXTRA_FLAGS="-DFOO=1" builds libfemtc_b200_x.so next to the
+# product library (own object cache) for A/B timing of compile-time variants (tools/quick_bench.py --lib)
+SUFFIX = os.environ.get("FEMTC_LIB_SUFFIX", "")
+OBJ = CSRC / ("_obj" + SUFFIX)
+LIB = PKG / f"libfemtc_b200{SUFFIX}.so"
 SOURCES = ["api.cu", "generic_kernels.cu", "tiled_kernels.cu", "column_kernels.cu", "cell_kernels.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
@@ -23,7 +26,7 @@ FLAGS = [
     "-std=c++17", "-O3", "-lineinfo",
     "-Xcompiler", "-fPIC,-Wall,-Wextra",
     "--expt-relaxed-constexpr",
-]
+] + os.environ.get("FEMTC_EXTRA_FLAGS", "").split()
 
 
 def _headers():
