@@ -34,8 +34,10 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static std::atomic<long long> g_opt_kernel{0};
 static std::atomic<long long> g_opt_host_chunk_mb{64};
 static std::atomic<long long> g_opt_variant{0};
+static std::atomic<long long> g_opt_tc{-1};
 
 long long opt_variant() { return g_opt_variant.load(); }
+long long opt_tc() { return g_opt_tc.load(); }
 
 // ---- device bookkeeping ---------------------------------------------------------------------
 static int g_sm_count[64];
@@ -138,6 +140,8 @@ static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T
     if (n == 0)
       n = launch_mass_tiled<T>(a);
     if (n == 0)
+      n = launch_mass_tc<T>(a);
+    if (n == 0)
       n = launch_mass_column<T>(a);
     if (n < 0)
       return (int)-n;
@@ -207,6 +211,8 @@ static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, co
     long long n = launch_stiffness_cell<T>(a);
     if (n == 0)
       n = launch_stiffness_tiled<T>(a);
+    if (n == 0)
+      n = launch_stiffness_tc<T>(a);
     if (n == 0)
       n = launch_stiffness_column<T>(a);
     if (n < 0)
@@ -699,6 +705,8 @@ int femtc_set_option(const char* name, long long value)
     g_opt_host_chunk_mb = value;
   else if (!std::strcmp(name, "variant"))
     g_opt_variant = value;
+  else if (!std::strcmp(name, "tc") && value >= -1 && value <= 1)
+    g_opt_tc = value;
   else
   {
     set_error("unknown option or value out of range");
@@ -716,6 +724,8 @@ long long femtc_get_option(const char* name)
     return g_opt_host_chunk_mb;
   if (!std::strcmp(name, "variant"))
     return g_opt_variant;
+  if (!std::strcmp(name, "tc"))
+    return g_opt_tc;
   if (!std::strcmp(name, "launches"))
     return g_launches;
   return -1;

@@ -90,6 +90,11 @@ template <typename T>
 long long launch_mass_cell(const MassArgs<T>& a);
 template <typename T>
 long long launch_stiffness_cell(const StiffnessArgs<T>& a);
+// tc_kernels.cu -- DMMA tensor-core family, fp64 n1 = 6..9 (mass, stiffness REF_EXACT); same convention
+template <typename T>
+long long launch_mass_tc(const MassArgs<T>& a);
+template <typename T>
+long long launch_stiffness_tc(const StiffnessArgs<T>& a);
 int tiled_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8]);
 
 int sm_count();

@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--max-gb", type=float, default=60.0)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--tc", type=int, default=-1, help="tensor-core family: 0 off, 1 on, -1 library default")
     ap.add_argument("--configs", default="", help="explicit list op:dtype:P:mode[,...] instead of the cross product")
     a = ap.parse_args()
     if a.configs:
@@ -59,6 +60,7 @@ def main():
 def sweep(a, ops, dtypes, degrees, modes):
     peak = peak_gbs()
     femtc.set_option("kernel", a.kernel)
+    femtc.set_option("tc", a.tc)
     rng = np.random.default_rng(1)
     for op in ops:
         for dt in dtypes:
