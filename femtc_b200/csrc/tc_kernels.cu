@@ -584,25 +584,38 @@ long long run_tc(const double* A, const double* D, const double* U, double* W, c
   return ncells;
 }
 
+// NGS = geometry ring slots per warp, NW = warps per cell.  Defaults are the measured best
+// (profiles/r01_tc_sweep.txt); `variant` (development knob) picks alternatives.
 template <int OP>
 long long run_tc_n1(int n1, const double* A, const double* D, const double* U, double* W, const double* geom,
                     size_t num_cells, cudaStream_t stream)
 {
-  // NGS = ring slots per warp (stiffness), NW = warps per cell; variant (development knob) picks alternatives
-  constexpr int NGS = OP == TC_STIFF ? 2 : 2;
   const long long v = opt_variant();
-  switch (n1)
+  if constexpr (OP == TC_MASS)
   {
-  case 6: return run_tc<6, OP, NGS, 2>(A, D, U, W, geom, num_cells, stream);
-  case 7: return v == 1 ? run_tc<7, OP, NGS, 2>(A, D, U, W, geom, num_cells, stream)
-                        : run_tc<7, OP, NGS, 4>(A, D, U, W, geom, num_cells, stream);
-  case 8: return v == 1 ? run_tc<8, OP, NGS, 2>(A, D, U, W, geom, num_cells, stream)
-               : v == 2 ? run_tc<8, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
-                        : run_tc<8, OP, NGS, 4>(A, D, U, W, geom, num_cells, stream);
-  case 9: return v == 1 ? run_tc<9, OP, NGS, 2>(A, D, U, W, geom, num_cells, stream)
-               : v == 2 ? run_tc<9, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
-                        : run_tc<9, OP, NGS, 4>(A, D, U, W, geom, num_cells, stream);
-  default: return 0;
+    switch (n1)
+    {
+    case 6: return run_tc<6, OP, 2, 2>(A, D, U, W, geom, num_cells, stream);
+    case 7: return run_tc<7, OP, 2, 2>(A, D, U, W, geom, num_cells, stream);
+    case 8: return v == 1 ? run_tc<8, OP, 2, 4>(A, D, U, W, geom, num_cells, stream)
+                          : run_tc<8, OP, 2, 1>(A, D, U, W, geom, num_cells, stream);
+    case 9: return run_tc<9, OP, 2, 4>(A, D, U, W, geom, num_cells, stream);
+    default: return 0;
+    }
+  }
+  else
+  {
+    switch (n1)
+    {
+    case 6: return run_tc<6, OP, 3, 2>(A, D, U, W, geom, num_cells, stream);
+    case 7: return v == 1 ? run_tc<7, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
+                          : run_tc<7, OP, 3, 4>(A, D, U, W, geom, num_cells, stream);
+    case 8: return v == 1 ? run_tc<8, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
+                          : run_tc<8, OP, 3, 4>(A, D, U, W, geom, num_cells, stream);
+    case 9: return v == 1 ? run_tc<9, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
+                          : run_tc<9, OP, 2, 4>(A, D, U, W, geom, num_cells, stream);
+    default: return 0;
+    }
   }
 }
 
@@ -619,6 +632,8 @@ long long launch_mass_tc(const MassArgs<T>& a)
     const long long tc = opt_tc();
     if (tc == 0 || n1 < 6 || n1 > 9)
       return 0;
+    if (tc < 0 && n1 != 8) // measured: only n1 = 8 beats the column kernel (71 % vs 59 % of the HBM peak)
+      return 0;
     return run_tc_n1<TC_MASS>(n1, a.phi_host, a.phi_host, a.U, a.W, a.detJ, a.num_cells, a.stream);
   }
   return 0;
@@ -632,6 +647,8 @@ long long launch_stiffness_tc(const StiffnessArgs<T>& a)
     const int n1 = a.degree + 1;
     const long long tc = opt_tc();
     if (tc == 0 || n1 < 6 || n1 > 9 || a.mode != FEMTC_STIFFNESS_REF_EXACT)
+      return 0;
+    if (tc < 0 && n1 < 7) // measured: n1 = 7, 8, 9 gain 12 / 20 / 4 points over the column kernel, n1 = 6 loses one
       return 0;
     return run_tc_n1<TC_STIFF>(n1, a.A_host, a.D_host, a.U, a.W, a.G, a.num_cells, a.stream);
   }

@@ -172,6 +172,10 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
 /* Tuning / introspection knobs, by name.  Unknown names return FEMTC_ERR_ARG / -1.
  *   "kernel"          0 = automatic, 1 = force the generic kernel, 2 = force the tiled kernel
  *   "host_chunk_mb"   input megabytes per pipelined chunk of the host-pointer path
+ *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
+ *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
+ *   "variant"         development knob: alternative pipeline depths of a kernel family (0 = tuned default;
+ *                     9 = one-thread-per-cell family off).  Results never depend on it.
  *   "launches"        (read-only) kernels launched by this library so far in this process */
 int femtc_set_option(const char* name, long long value);
 long long femtc_get_option(const char* name);

@@ -366,3 +366,67 @@ def test_unchanged_reference_benches_run():
     r = subprocess.run([str(BIN / "bench_mass"), "1000000", "3", "ikj", "5", "0", "double"],
                        capture_output=True, text=True, timeout=600)
     assert "Block size not supported" in r.stdout            # reference behaviour: message, no throw
+
+
+# ---- every kernel family against the oracle, whichever one the dispatcher would pick by default -----------
+# tc: 1 = DMMA tensor-core family wherever applicable (fp64, degrees 5..8, mass / REF_EXACT), 0 = never.
+# variant 9 = cell family (one thread per cell, degrees 1..2) off -> slab / column kernels serve those shapes;
+# variants 1, 2 = alternative pipeline depths of the cell and tensor-core families.
+@pytest.mark.parametrize("tc", (0, 1))
+@pytest.mark.parametrize("P", (5, 6, 7, 8))
+@pytest.mark.parametrize("op", ("mass", "stiffness"))
+def test_tensor_core_family_parity(femtc, oracle, torch_cuda, op, P, tc):
+    nc = {5: 263, 6: 131, 7: 68, 8: 37}[P]  # odd counts: the skewed-copy families leave one cell to the tail kernel
+    femtc.set_option("tc", tc)
+    try:
+        for centred in (False, True):
+            phi, U, geom = splitmix(oracle, op, P, nc, "float64", seed=77 + P, centred=centred)
+            ref = oracle_run(oracle, op, phi, U, geom, P, 0)
+            W = run_device(femtc, torch_cuda, op, phi, U, geom, P, 0)
+            assert np.isfinite(W).all()
+            err = rel_err(W, ref) if centred else elementwise_rel_err(W, ref)
+            assert err <= TOL["float64"], (op, P, tc, centred, err)
+    finally:
+        femtc.set_option("tc", -1)
+
+
+@pytest.mark.parametrize("variant", (1, 2, 9))
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", (1, 2, 7, 8))
+@pytest.mark.parametrize("op,mode", CASES)
+def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, variant):
+    nc = {1: 4099, 2: 2053, 7: 67, 8: 37}[P]
+    femtc.set_option("variant", variant)
+    try:
+        phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=3 + P, centred=True)
+        ref = oracle_run(oracle, op, phi, U, geom, P, mode)
+        W = run_device(femtc, torch_cuda, op, phi, U, geom, P, mode)
+        assert rel_err(W, ref) <= TOL[dt], (op, mode, P, dt, variant)
+    finally:
+        femtc.set_option("variant", 0)
+
+
+def test_tensor_core_large_batch_matches_column_kernel(femtc, torch_cuda):
+    """Same inputs through the DMMA family and the FMA column family at a size with many blocks per SM and
+    a ring that wraps: the two must agree to rounding (1e-13) on every one of the 20 000 cells."""
+    from femtc_b200.distributed import fill_uniform
+    torch = torch_cuda
+    for op, P in (("stiffness", 7), ("stiffness", 8), ("mass", 7), ("mass", 8)):
+        nd, nc = (P + 1) ** 3, 20000
+        gw = 6 if op == "stiffness" else 1
+        phi = np.random.default_rng(P).random(2 * (P + 1) ** 2)
+        U = fill_uniform(torch.empty(nc * nd, dtype=torch.float64, device="cuda"), 1, 1)
+        G = fill_uniform(torch.empty(nc * nd * gw, dtype=torch.float64, device="cuda"), 1, 2)
+        out = []
+        for tc in (1, 0):
+            femtc.set_option("tc", tc)
+            W = torch.full_like(U, float("nan"))
+            rc = (femtc.mass_operator(phi, U, W, G, nc, P) if op == "mass"
+                  else femtc.stiffness_operator(phi, U, W, G, nc, P, mode=0))
+            assert rc == 0
+            torch.cuda.synchronize()
+            out.append(W)
+        femtc.set_option("tc", -1)
+        assert torch.isfinite(out[0]).all()
+        err = float(((out[0] - out[1]).abs() / out[1].abs().max()).max())
+        assert err < 1e-13, (op, P, err)
