@@ -52,6 +52,10 @@ def parse_args():
     ap.add_argument("--dtype", default="f64", choices=("f64", "f32"))
     ap.add_argument("--mode", default="ref_exact", choices=("ref_exact", "full"))
     ap.add_argument("--cells", type=int, default=1_000_000, help="cells per GPU")
+    ap.add_argument("--total-cells", type=int, default=0,
+                    help="strong scaling (BASELINE config 5): this many cells in total, partitioned over the GPUs; "
+                         "a rank whose share exceeds --resident-gb sweeps it in resident chunks")
+    ap.add_argument("--resident-gb", type=float, default=72.0, help="per-GPU field bytes held at a time with --total-cells")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -173,6 +177,107 @@ def run_reference(a, rank: int):
 
 
 # ------------------------------------------------------------------------------------------------------
+def run_strong(a, rank: int, local_rank: int, world: int):
+    """BASELINE config 5: a fixed global batch (--total-cells) partitioned over the GPUs, no halo.  A rank holds
+    at most --resident-gb of fields; a larger share is swept in chunks (inputs regenerated on the device between
+    chunks, outside the timed spans).  Timed: the operator launches only (CUDA events per chunk, summed; max over
+    ranks).  The one collective is the 4-double checksum all-gather at the end."""
+    import torch
+    import torch.distributed as dist
+
+    import femtc_b200 as femtc
+    from femtc_b200 import _lib
+    from femtc_b200.distributed import combine_checksums, device_checksum, fill_uniform, partition
+
+    torch.cuda.set_device(local_rank)
+    _lib.check(_lib.lib.femtc_set_device(local_rank))
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    P, nd, gw = a.degree, (a.degree + 1) ** 3, OPS[a.op]
+    tdt = torch.float64 if a.dtype == "f64" else torch.float32
+    ndt = np.float64 if a.dtype == "f64" else np.float32
+    size = 8 if a.dtype == "f64" else 4
+    mode = femtc.FULL if a.mode == "full" else femtc.REF_EXACT
+    lo, hi = partition(a.total_cells, rank, world)
+    bytes_per_cell = nd * (2 + gw) * size
+    chunk = max(32, int(a.resident_gb * 1e9 / bytes_per_cell) // 32 * 32)
+    chunk = min(chunk, hi - lo)
+    n2 = (P + 1) ** 2
+    phi = fill_uniform(torch.empty(2 * n2, dtype=tdt, device=dev), 1, 0, 0).cpu().numpy().astype(ndt)
+
+    def up(n):
+        return (n + 31) // 32 * 32
+    nU, nG = chunk * nd, chunk * nd * gw
+    arena = torch.empty(up(nU) + up(nG) + up(nU), dtype=tdt, device=dev)
+    U, G, W = arena[:nU], arena[up(nU):up(nU) + nG], arena[up(nU) + up(nG):up(nU) + up(nG) + nU]
+
+    def apply(n):
+        rc = (femtc.mass_operator(phi, U, W, G, n, P) if a.op == "mass"
+              else femtc.stiffness_operator(phi, U, W, G, n, P, mode=mode))
+        assert rc == 0
+
+    def sweep(reps_per_chunk, timed):
+        """one pass over the rank's cells; returns (kernel ms, checksum partials)"""
+        ms, parts = 0.0, []
+        for c0 in range(lo, hi, chunk):
+            n = min(chunk, hi - c0)
+            fill_uniform(U[:n * nd], 1, 1, c0 * nd)
+            fill_uniform(G[:n * nd * gw], 1, 2, c0 * nd * gw)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps_per_chunk):
+                apply(n)
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1) / reps_per_chunk
+            if timed:
+                parts.append(device_checksum(W[:n * nd]).cpu().numpy())
+        return ms, parts
+
+    sweep(max(1, min(a.warmup, 3)), False)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    launches0 = femtc.get_option("launches")
+    with ClockSampler(local_rank) as clocks:
+        ms, parts = sweep(a.steps, True)
+    launches = femtc.get_option("launches") - launches0
+    loc = np.array([sum(p[0] for p in parts), sum(p[1] for p in parts), max(p[2] for p in parts), sum(p[3] for p in parts)])
+    loc_t = torch.tensor(loc, dtype=torch.float64, device=dev)
+    glob = combine_checksums(loc_t) if world > 1 else loc_t
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item()
+    if rank == 0:
+        peak, peak_src = peaks()
+        dofs = a.total_cells * nd
+        achieved = (hi - lo) * nd * (2 + gw) * size / (ms_step * 1e-3) / 1e9
+        cs = [float(x) for x in glob.cpu().numpy()]
+        print(json.dumps({
+            "metric": METRIC, "value": dofs / ms_step / 1e6, "unit": "GDoF/s", "n_gpus": world, "steps": a.steps,
+            "warmup": max(1, min(a.warmup, 3)), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"workload": f"stiffness action degree {P}, {a.dtype}, {a.total_cells} cells in total partitioned over "
+                                   f"{world} B200 with NCCL checksum reduction" if a.op == "stiffness" else
+                                   f"mass action degree {P}, {a.dtype}, {a.total_cells} cells in total over {world} B200",
+                       "op": a.op, "degree": P, "mode": a.mode, "total_cells": a.total_cells, "cells_this_rank": hi - lo,
+                       "resident_chunk_cells": chunk, "chunks_per_rank": -(-(hi - lo) // chunk), "dofs_per_step": dofs,
+                       "timed": "operator launches only, CUDA events per resident chunk summed, max over ranks; inputs are "
+                                "regenerated on the device between chunks outside the timed spans",
+                       "l2": f"no flush needed: every chunk streams {chunk * bytes_per_cell / 1e9:.1f} GB"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_dof": (2 + gw) * size},
+            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(),
+            "checksum": {"sum": cs[0], "sum_sq": cs[1], "max_abs": cs[2], "n": cs[3]},
+        }), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_ours(a, rank: int, local_rank: int, world: int):
     import torch
     import torch.distributed as dist
@@ -376,7 +481,10 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", str(Path(__file__).resolve())] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
-    run_ours(a, rank, local_rank, world)
+    if a.total_cells:
+        run_strong(a, rank, local_rank, world)
+    else:
+        run_ours(a, rank, local_rank, world)
 
 
 if __name__ == "__main__":
