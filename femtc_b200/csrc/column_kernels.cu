@@ -551,21 +551,27 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   const int my_off = up16(RB * (my_qs - q0)) + (SC::F32 ? 32 * my_k : 0) + RB * (te - my_qs);
 
   const long long my_tiles = (long long)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  const long long q_end = my_tiles * N1;
 
-  auto load_plane = [&](long long q, int slot)
+  // Ring bookkeeping without any division: the issue side runs exactly NG planes ahead of the consume
+  // side, so while plane i0 of a tile is consumed the plane to request is i0 + NG of the same tile, or
+  // i0 + NG - N1 of the block's next tile -- a compile-time distinction wherever the plane loop is
+  // unrolled.  Only (slot, parity) and one byte pointer per tile are carried.
+  static_assert(NG <= N1, "the geometry ring may run at most one tile ahead");
+  const unsigned char* g_tile = reinterpret_cast<const unsigned char*>(Gm) +
+                                ((size_t)blockIdx.x * C * ND + is_rec) * RB;   // my piece, plane 0, current tile
+  const size_t g_stride = (size_t)gridDim.x * C * ND * RB;                      // to the block's next tile
+  const int is_par = SC::F32 ? (is_rec & 1) : 0;              // tile bases are even record counts
+  const uint32_t is_bytes0 = (uint32_t)up16(RB * is_cnt), is_bytes1 = (uint32_t)up16(RB * is_cnt + 8);
+  const uint32_t is_dst_u32 = smem_u32(gRing) + is_dst;
+
+  auto request_plane = [&](int plane, int slot, const unsigned char* tile_src)
   {
     if (issuer)
     {
-      const long long t = blockIdx.x + (q / N1) * (long long)gridDim.x;
-      const int plane = (int)(q % N1);
-      const int rec = is_rec + plane * N2;
-      const int sh = SC::F32 ? (rec & 1) : 0;                 // tile bases are even record counts
-      const uint32_t bytes = (uint32_t)up16(RB * is_cnt + 8 * sh);
-      const unsigned char* src = reinterpret_cast<const unsigned char*>(Gm) +
-                                 ((size_t)t * C * ND + rec) * RB - 8 * sh;
+      const int sh = SC::F32 ? ((is_par + plane * (N2 & 1)) & 1) : 0;
+      const uint32_t bytes = sh ? is_bytes1 : is_bytes0;
       mbar_expect_tx(barG + 8 * slot, bytes);
-      bulk_g2s(smem_u32(gRing + slot * SC::slot_bytes + is_dst), src, bytes, barG + 8 * slot);
+      bulk_g2s(is_dst_u32 + slot * SC::slot_bytes, tile_src + plane * (N2 * RB) - 8 * sh, bytes, barG + 8 * slot);
     }
   };
 
@@ -587,9 +593,11 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
     mbar_expect_tx(barU, G::tile_bytes);
     bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
   }
-  long long q_issue = 0, q = 0;
-  for (; q_issue < NG && q_issue < q_end; ++q_issue)
-    load_plane(q_issue, (int)(q_issue % NG));
+  if (my_tiles > 0)
+    for (int s = 0; s < NG; ++s)
+      request_plane(s, s, g_tile);
+  int c_slot = 0;
+  uint32_t c_par = 0;
 
   uint32_t phase = 0;
   for (; tile < ntiles; tile += gridDim.x, phase ^= 1)
@@ -678,7 +686,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
           h0[i] = h1[i] = T(0);
       }
 #pragma unroll(Roll<T, N1>::in)
-      for (int i0 = 0; i0 < N1; ++i0, ++q)
+      for (int i0 = 0; i0 < N1; ++i0)
       {
         const T w0 = row_dot(B.dt, i0, ta);
         const T w1 = row_dot(B.at, i0, td);
@@ -687,10 +695,9 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
           w2 = row_dot(B.at, i0, sa);
         else
           w2 = row_dot(B.at, i0, ta);
-        const int slot = (int)(q % NG);
-        mbar_wait(barG + 8 * slot, (uint32_t)((q / NG) & 1));
+        mbar_wait(barG + 8 * c_slot, c_par);
         const int sh = SC::F32 ? ((my_par + i0 * (N2 & 1)) & 1) : 0;
-        const T* gp = reinterpret_cast<const T*>(gRing + slot * SC::slot_bytes + my_off + 8 * sh);
+        const T* gp = reinterpret_cast<const T*>(gRing + c_slot * SC::slot_bytes + my_off + 8 * sh);
         T g[6];
         if constexpr (sizeof(T) == 8)
         {
@@ -729,10 +736,14 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         // REF_EXACT: only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
         col_axpy(B.a, i0, f2, h2);                              // A0 f2
         __syncwarp(); // every lane is done with this slot: request the chunk NG ahead into it
-        if (q_issue < q_end)
+        if (i0 + NG < N1)
+          request_plane(i0 + NG, c_slot, g_tile);
+        else if (tn < ntiles)
+          request_plane(i0 + NG - N1, c_slot, g_tile + g_stride);
+        if (++c_slot == NG)
         {
-          load_plane(q_issue, slot);
-          ++q_issue;
+          c_slot = 0;
+          c_par ^= 1;
         }
       }
       if constexpr (!FULL)
@@ -745,6 +756,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         col_store<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), h2);
       }
     }
+    g_tile += g_stride;
     __syncthreads(); // (3)
     // ---- phase B': back along axis 1 --------------------------------------------------------------------------
     {
