@@ -5,12 +5,12 @@ interface used by the tests and by bench.py."""
 from . import _lib
 from ._lib import FemtcError, get_option, kernel_info, last_error, set_option
 from .linalg import Order, gemm_blocked, gemm_micro, string2order
-from .operators import FULL, REF_EXACT, mass_operator, stiffness_operator
+from .operators import FULL, REF_EXACT, ResidentOperator, mass_operator, stiffness_operator
 from .tmm import apply_contractions
 
 __all__ = [
     "FemtcError", "Order", "string2order", "gemm_blocked", "gemm_micro", "mass_operator",
-    "stiffness_operator", "apply_contractions", "REF_EXACT", "FULL", "set_option", "get_option",
+    "stiffness_operator", "ResidentOperator", "apply_contractions", "REF_EXACT", "FULL", "set_option", "get_option",
     "kernel_info", "last_error", "device",
 ]
 

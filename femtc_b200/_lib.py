@@ -40,6 +40,13 @@ def _load() -> C.CDLL:
         getattr(lib, f"femtc_apply_contractions_{s}").argtypes = [i] * 3 + [vp] * 5 + [sz]
         getattr(lib, f"femtc_checksum_device_{s}").argtypes = [vp, sz, vp, vp]
         getattr(lib, f"femtc_fill_uniform_device_{s}").argtypes = [vp, sz, u64, u64, u64, i, vp]
+        getattr(lib, f"femtc_operator_create_{s}").argtypes = [C.POINTER(vp), i, vp, sz, vp, sz, i, i]
+    lib.femtc_operator_apply.argtypes = [vp, vp, vp]
+    lib.femtc_operator_apply_device.argtypes = [vp, vp, vp, vp]
+    lib.femtc_operator_device_bytes.argtypes = [vp]
+    lib.femtc_operator_device_bytes.restype = sz
+    lib.femtc_operator_destroy.argtypes = [vp]
+    lib.femtc_operator_destroy.restype = None
     lib.femtc_string2order.argtypes = [C.c_char_p]
     lib.femtc_set_device.argtypes = [i]
     lib.femtc_last_error.restype = C.c_char_p

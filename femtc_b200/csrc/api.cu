@@ -269,9 +269,10 @@ static int ensure(void*& p, size_t& cap, size_t bytes)
   return FEMTC_OK;
 }
 
+// `geom_dev` != nullptr: the geometry already lives in HBM (operator handle, below); only U and W travel.
 template <typename T, typename Launch>
 static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t num_cells, size_t nd,
-                         Launch&& launch)
+                         Launch&& launch, const T* geom_dev = nullptr)
 {
   int dev = 0;
   FEMTC_CUDA(cudaGetDevice(&dev));
@@ -283,7 +284,7 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
       FEMTC_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     cache.streams_ready = true;
   }
-  const size_t bytes_per_cell = nd * sizeof(T) * (1 + geom_width);
+  const size_t bytes_per_cell = nd * sizeof(T) * (1 + (geom_dev ? 0 : geom_width));
   size_t chunk_cells = std::max<size_t>(1, ((size_t)g_opt_host_chunk_mb.load() << 20) / bytes_per_cell);
   // keep chunk boundaries 16-byte aligned in every array so the TMA path applies to all chunks
   chunk_cells = std::max<size_t>(16, chunk_cells & ~size_t(15));
@@ -299,14 +300,15 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
     FEMTC_CUDA(cudaStreamSynchronize(s.stream));
     if ((rc = ensure(s.dU, s.capU, chunk_cells * nd * sizeof(T))))
       break;
-    if ((rc = ensure(s.dG, s.capG, chunk_cells * nd * geom_width * sizeof(T))))
+    if (!geom_dev && (rc = ensure(s.dG, s.capG, chunk_cells * nd * geom_width * sizeof(T))))
       break;
     if ((rc = ensure(s.dW, s.capW, chunk_cells * nd * sizeof(T))))
       break;
     FEMTC_CUDA(cudaMemcpyAsync(s.dU, U + c0 * nd, n * nd * sizeof(T), cudaMemcpyHostToDevice, s.stream));
-    FEMTC_CUDA(cudaMemcpyAsync(s.dG, geom + c0 * nd * geom_width, n * nd * geom_width * sizeof(T),
-                               cudaMemcpyHostToDevice, s.stream));
-    rc = launch((const T*)s.dU, (T*)s.dW, (const T*)s.dG, n, s.stream);
+    if (!geom_dev)
+      FEMTC_CUDA(cudaMemcpyAsync(s.dG, geom + c0 * nd * geom_width, n * nd * geom_width * sizeof(T),
+                                 cudaMemcpyHostToDevice, s.stream));
+    rc = launch((const T*)s.dU, (T*)s.dW, geom_dev ? geom_dev + c0 * nd * geom_width : (const T*)s.dG, n, s.stream);
     if (rc)
       break;
     FEMTC_CUDA(cudaMemcpyAsync(W + c0 * nd, s.dW, n * nd * sizeof(T), cudaMemcpyDeviceToHost, s.stream));
@@ -501,6 +503,119 @@ static int apply_contractions_host(int Na, int Nb, int Tr, const T* I0, const T*
   return FEMTC_OK;
 }
 
+// ---- operator handle: geometry resident in HBM ------------------------------------------------------
+// In a matrix-free solver detJ / G are set-up data: the reference's benches apply the operator `nreps`
+// times to the same arrays (bench_mass.cpp:95-105, bench_stiffness.cpp:95-105).  A handle uploads the
+// geometry once; an application then moves only U in and W out (2 of the 3 / 8 words per DoF).
+struct Operator
+{
+  int kind = 0;        // 0 mass, 1 stiffness
+  int tsize = 8;       // sizeof(T)
+  int degree = 0;
+  int mode = 0;
+  int device = 0;
+  size_t num_cells = 0;
+  size_t phi_len = 0;
+  std::vector<unsigned char> phi; // host copy of the tables (they travel as kernel parameters)
+  void* dGeom = nullptr;
+  size_t geom_bytes = 0;
+};
+
+template <typename T>
+static int operator_create(Operator** out, int kind, const T* phi, size_t phi_len, const T* geom, size_t num_cells,
+                           int degree, int mode)
+{
+  if (out)
+    *out = nullptr;
+  if (!out || !phi || (kind != 0 && kind != 1) || (num_cells && !geom))
+  {
+    set_error("femtc_operator_create: null pointer or unknown operator kind");
+    return FEMTC_ERR_ARG;
+  }
+  if (degree < 1 || degree > 25)
+  {
+    set_error("degree not supported");
+    return FEMTC_ERR_DEGREE;
+  }
+  if (kind == 1 && mode != FEMTC_STIFFNESS_REF_EXACT && mode != FEMTC_STIFFNESS_FULL)
+  {
+    set_error("unknown stiffness mode");
+    return FEMTC_ERR_MODE;
+  }
+  const size_t n1 = degree + 1, n2 = n1 * n1, nd = n2 * n1;
+  if (phi_len < n2)
+  {
+    set_error("phi shorter than (degree+1)^2");
+    return FEMTC_ERR_LENGTH;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  Operator* op = new Operator;
+  op->kind = kind, op->tsize = (int)sizeof(T), op->degree = degree, op->mode = kind ? mode : 0;
+  op->num_cells = num_cells;
+  op->phi_len = std::min(phi_len, 2 * n2);
+  op->phi.assign(reinterpret_cast<const unsigned char*>(phi),
+                 reinterpret_cast<const unsigned char*>(phi) + op->phi_len * sizeof(T));
+  op->geom_bytes = num_cells * nd * (kind ? 6 : 1) * sizeof(T);
+  cudaError_t e = cudaGetDevice(&op->device);
+  if (e == cudaSuccess && op->geom_bytes)
+    e = cudaMalloc(&op->dGeom, op->geom_bytes);
+  if (e == cudaSuccess && op->geom_bytes)
+    e = cudaMemcpy(op->dGeom, geom, op->geom_bytes, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess)
+  {
+    if (op->dGeom)
+      cudaFree(op->dGeom);
+    delete op;
+    return cuda_fail(e, "femtc_operator_create (geometry upload)", __FILE__, __LINE__);
+  }
+  *out = op;
+  return FEMTC_OK;
+}
+
+template <typename T>
+static int operator_apply_device_t(const Operator* op, const T* dU, T* dW, size_t first_cell, size_t n, cudaStream_t s)
+{
+  const T* phi = reinterpret_cast<const T*>(op->phi.data());
+  const size_t n1 = op->degree + 1, nd = n1 * n1 * n1;
+  const T* g = reinterpret_cast<const T*>(op->dGeom) + first_cell * nd * (op->kind ? 6 : 1);
+  if (op->kind == 0)
+    return mass_device<T>(phi, op->phi_len, dU, dW, g, n, op->degree, s);
+  return stiffness_device<T>(phi, op->phi_len, dU, dW, g, n, op->degree, op->mode, s);
+}
+
+template <typename T>
+static int operator_apply_host_t(const Operator* op, const T* U, T* W)
+{
+  const size_t n1 = op->degree + 1, nd = n1 * n1 * n1;
+  return host_pipeline<T>(U, W, (const T*)nullptr, op->kind ? 6 : 1, op->num_cells, nd,
+                          [&](const T* dU, T* dW, const T* dG, size_t n, cudaStream_t s)
+                          {
+                            const T* phi = reinterpret_cast<const T*>(op->phi.data());
+                            if (op->kind == 0)
+                              return mass_device<T>(phi, op->phi_len, dU, dW, dG, n, op->degree, s);
+                            return stiffness_device<T>(phi, op->phi_len, dU, dW, dG, n, op->degree, op->mode, s);
+                          },
+                          reinterpret_cast<const T*>(op->dGeom));
+}
+
+static int operator_check(const Operator* op, const void* U, const void* W)
+{
+  if (!op || (op->num_cells && (!U || !W)))
+  {
+    set_error("femtc_operator_apply: null handle or pointer");
+    return FEMTC_ERR_ARG;
+  }
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev != op->device)
+  {
+    set_error("femtc_operator_apply: the handle belongs to another device than the calling thread's current one");
+    return FEMTC_ERR_ARG;
+  }
+  return FEMTC_OK;
+}
+
 } // namespace femtc
 
 // ================================ extern "C" =====================================================
@@ -588,6 +703,50 @@ int femtc_apply_contractions_f32(int Na, int Nb, int Tr, const float* I0, const 
                                  const float* B, float* A, size_t batch)
 {
   return apply_contractions_host<float>(Na, Nb, Tr, I0, I1, I2, B, A, batch);
+}
+
+struct femtc_operator; /* opaque: femtc::Operator */
+int femtc_operator_create_f64(femtc_operator** op, int kind, const double* phi, size_t phi_len, const double* geom,
+                              size_t num_cells, int degree, int mode)
+{
+  return operator_create<double>(reinterpret_cast<Operator**>(op), kind, phi, phi_len, geom, num_cells, degree, mode);
+}
+int femtc_operator_create_f32(femtc_operator** op, int kind, const float* phi, size_t phi_len, const float* geom,
+                              size_t num_cells, int degree, int mode)
+{
+  return operator_create<float>(reinterpret_cast<Operator**>(op), kind, phi, phi_len, geom, num_cells, degree, mode);
+}
+int femtc_operator_apply(femtc_operator* h, const void* U, void* W)
+{
+  const Operator* op = reinterpret_cast<const Operator*>(h);
+  int rc = operator_check(op, U, W);
+  if (rc || op->num_cells == 0)
+    return rc;
+  return op->tsize == 8 ? operator_apply_host_t<double>(op, (const double*)U, (double*)W)
+                        : operator_apply_host_t<float>(op, (const float*)U, (float*)W);
+}
+int femtc_operator_apply_device(femtc_operator* h, const void* dU, void* dW, void* stream)
+{
+  const Operator* op = reinterpret_cast<const Operator*>(h);
+  int rc = operator_check(op, dU, dW);
+  if (rc || op->num_cells == 0)
+    return rc;
+  return op->tsize == 8
+             ? operator_apply_device_t<double>(op, (const double*)dU, (double*)dW, 0, op->num_cells, (cudaStream_t)stream)
+             : operator_apply_device_t<float>(op, (const float*)dU, (float*)dW, 0, op->num_cells, (cudaStream_t)stream);
+}
+size_t femtc_operator_device_bytes(const femtc_operator* h)
+{
+  return h ? reinterpret_cast<const Operator*>(h)->geom_bytes : 0;
+}
+void femtc_operator_destroy(femtc_operator* h)
+{
+  Operator* op = reinterpret_cast<Operator*>(h);
+  if (!op)
+    return;
+  if (op->dGeom)
+    cudaFree(op->dGeom);
+  delete op;
 }
 
 int femtc_string2order(const char* name)

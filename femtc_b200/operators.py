@@ -143,3 +143,64 @@ def _knob_code(degree, order, Mb, Nb) -> int:
     if not 1 <= degree <= 25:
         return _lib.ERR_DEGREE
     return _lib.OK
+
+
+class ResidentOperator:
+    """Operator handle with the geometry resident in HBM (femtc_operator_* in include/femtc_b200.h).
+
+    The reference's drivers re-apply the operator to the same detJ / G (bench_mass.cpp:95-105,
+    bench_stiffness.cpp:95-105); a handle uploads them once, `apply` then moves only U and W.
+    kind: "mass" (geom = detJ) or "stiffness" (geom = G).  `geom` is a host numpy array."""
+
+    def __init__(self, kind: str, phi, geom, num_cells: int, degree: int, mode: int = REF_EXACT):
+        import ctypes as C
+        if kind not in ("mass", "stiffness"):
+            raise ValueError("kind must be 'mass' or 'stiffness'")
+        phi = _phi_host(phi)
+        s = _suffix_np(phi.dtype)
+        self.kind, self.degree, self.num_cells, self.suffix = kind, int(degree), int(num_cells), s
+        if 1 <= degree <= 25:
+            need = int(num_cells) * (degree + 1) ** 3 * (6 if kind == "stiffness" else 1)
+            if geom.size < need:
+                raise ValueError(f"geometry holds {geom.size} values, {need} needed")
+        h = C.c_void_p()
+        rc = getattr(_lib.lib, f"femtc_operator_create_{s}")(
+            C.byref(h), 1 if kind == "stiffness" else 0, phi.ctypes.data, phi.size,
+            _ptr(geom, "geom", s), int(num_cells), int(degree), int(mode))
+        self._h = h if rc == 0 else None
+        if rc:
+            _finish(rc)
+            raise _lib.FemtcError(rc, _lib.last_error())
+
+    @property
+    def device_bytes(self) -> int:
+        return int(_lib.lib.femtc_operator_device_bytes(self._h))
+
+    def apply(self, U, W) -> int:
+        """W = op(U).  U, W both host arrays (synchronous, pipelined copies) or both CUDA tensors
+        (asynchronous on the current stream)."""
+        if self._h is None:
+            raise RuntimeError("operator handle was destroyed")
+        _check_sizes(self.num_cells, self.degree, (U, "U", 1), (W, "W", 1))
+        dev = [_is_device(x) for x in (U, W)]
+        if all(dev):
+            rc = _lib.lib.femtc_operator_apply_device(self._h, _ptr(U, "U", self.suffix), _ptr(W, "W", self.suffix),
+                                                      _current_stream())
+        elif not any(dev):
+            rc = _lib.lib.femtc_operator_apply(self._h, _ptr(U, "U", self.suffix), _ptr(W, "W", self.suffix))
+        else:
+            raise TypeError("U and W must both be host arrays or both be CUDA tensors")
+        return _finish(rc)
+
+    def destroy(self) -> None:
+        if getattr(self, "_h", None) is not None:
+            _lib.lib.femtc_operator_destroy(self._h)
+            self._h = None
+
+    __del__ = destroy
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.destroy()

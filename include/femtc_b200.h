@@ -102,6 +102,28 @@ int femtc_stiffness_apply_device_f32(const float* phi_host, size_t phi_len, cons
                                      float* dW, const float* dG, size_t num_cells, int degree,
                                      int mode, void* stream);
 
+/* ---- operator handle: geometry resident in HBM (set up once, apply many) ---------------
+ * The reference's drivers apply the operator nreps times to the SAME detJ / G
+ * (bench_mass.cpp:95-105, bench_stiffness.cpp:95-105); in a matrix-free solver these arrays are
+ * set-up data.  A handle uploads them once (num_cells*nd*{1|6} values, HOST pointer, copied --
+ * the caller may free `geom` after create) together with phi; an application then moves only U in
+ * and W out.  kind: 0 = mass (geom = detJ), 1 = stiffness (geom = G); mode: FEMTC_STIFFNESS_* (ignored
+ * for mass).  Same kernels, same results bit for bit as femtc_{mass,stiffness}_apply_*.
+ *   femtc_operator_apply         U, W HOST pointers (dtype of the handle), synchronous, pipelined
+ *                                H2D(U) -> kernel -> D2H(W) in chunks of "host_chunk_mb"
+ *   femtc_operator_apply_device  U, W DEVICE pointers, asynchronous on `stream`
+ * A handle is bound to the device that was current at creation; it may be applied from any
+ * thread whose current device is that one, but not concurrently with its own destruction. */
+typedef struct femtc_operator femtc_operator;
+int femtc_operator_create_f64(femtc_operator** op, int kind, const double* phi, size_t phi_len,
+                              const double* geom, size_t num_cells, int degree, int mode);
+int femtc_operator_create_f32(femtc_operator** op, int kind, const float* phi, size_t phi_len,
+                              const float* geom, size_t num_cells, int degree, int mode);
+int femtc_operator_apply(femtc_operator* op, const void* U, void* W);
+int femtc_operator_apply_device(femtc_operator* op, const void* dU, void* dW, void* stream);
+size_t femtc_operator_device_bytes(const femtc_operator* op); /* HBM held by the handle */
+void femtc_operator_destroy(femtc_operator* op);
+
 /* ---- small-GEMM layer, host pointers, synchronous ------------------------------------
  * Replaces linalg::gemm_blocked<T,k,m,n,order,MB,NB>(a,b,c) (reference src/linalg.hpp:101-182;
  * call sites tests/test_gemm.cpp:41,52): C(m x n, column-major ld=m) = A(m x k, column-major

@@ -88,6 +88,33 @@ def test_other_argument_errors(femtc):
         femtc.mass_operator(phi, U.astype(np.float32), W, U, 1, 3)
 
 
+def test_operator_handle_argument_errors_and_no_fallback(femtc):
+    """femtc_operator_* (resident geometry): argument validation happens before any device work, and
+    without a B200 creation fails loudly and leaves a null handle."""
+    import ctypes as C
+    from femtc_b200 import _lib
+    lib = _lib.lib
+    phi, G = np.ones(32), np.ones(6 * 64)
+    p = lambda a: a.ctypes.data
+    h = C.c_void_p(1234)
+    assert lib.femtc_operator_create_f64(C.byref(h), 2, p(phi), 32, p(G), 1, 3, 0) == _lib.ERR_ARG and not h.value
+    assert lib.femtc_operator_create_f64(C.byref(h), 1, p(phi), 32, p(G), 1, 0, 0) == _lib.ERR_DEGREE
+    assert lib.femtc_operator_create_f64(C.byref(h), 1, p(phi), 32, p(G), 1, 3, 7) == _lib.ERR_MODE
+    assert lib.femtc_operator_create_f64(C.byref(h), 0, p(phi), 15, p(G), 1, 3, 0) == _lib.ERR_LENGTH
+    assert lib.femtc_operator_create_f32(None, 0, p(phi), 16, p(G), 1, 3, 0) == _lib.ERR_ARG
+    assert lib.femtc_operator_apply(None, p(G), p(G)) == _lib.ERR_ARG
+    assert lib.femtc_operator_device_bytes(None) == 0
+    lib.femtc_operator_destroy(None)  # no-op
+    if femtc.device_count() == 0:
+        with pytest.raises(femtc.FemtcError) as e:
+            femtc.ResidentOperator("stiffness", phi, G, 1, 3)
+        assert e.value.code == 6 and "no CPU fallback" in str(e.value)
+    with pytest.raises(ValueError):
+        femtc.ResidentOperator("stiffness", phi, G, 2, 3)   # G too short for two cells
+    with pytest.raises(ValueError):
+        femtc.ResidentOperator("laplace", phi, G, 1, 3)
+
+
 def test_no_silent_cpu_fallback(femtc):
     """Without a B200 every compute entry point must fail loudly, never compute on the host."""
     if femtc.device_count() > 0:
@@ -106,6 +133,7 @@ CXX_TU = r"""
 #include "mass.hpp"
 #include "stiffness.hpp"
 #include "tmm.hpp"
+#include "resident_operator.hpp"
 #include "mass.hpp"      // include twice: the replacement headers are guarded (the reference's are not)
 template <typename T> int use()
 {
@@ -124,6 +152,16 @@ template <typename T> int use()
   contract<T, 4, 4, 4>(phi.data(), U.data(), W.data());
   transpose<T, 4, 4, 4, 16, 4, 1>(U.data(), W.data());
   transpose<T, 4, 4, 4, 1>(U.data(), W.data());
+  try
+  {
+    operators::ResidentOperator<T> K(operators::Kind::stiffness, phi, G, 1, 3, operators::StiffnessMode::full);
+    K.apply(U, W);
+    K.apply_device(nullptr, nullptr);
+    (void)K.device_bytes();
+  }
+  catch (const std::runtime_error&)
+  {
+  }
   return 0;
 }
 int main() { return use<double>() + use<float>(); }

@@ -117,6 +117,38 @@ def test_operator_parity_host_abi(femtc, oracle, op, mode, P, dt):
     assert rel_err(W, ref) <= TOL[dt]
 
 
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", (1, 3, 6))
+@pytest.mark.parametrize("op,mode", CASES)
+def test_resident_operator_matches_drop_in_entry_points(femtc, oracle, torch_cuda, op, mode, P, dt):
+    """femtc_operator_* (geometry uploaded once): host and device application equal the oracle within
+    tolerance and equal the drop-in entry point bit for bit, over several applications with new U."""
+    nc = {1: 5003, 3: 777, 6: 131}[P]
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=9, centred=True)
+    with femtc.ResidentOperator(op, phi, geom, nc, P, mode=mode) as K:
+        assert K.device_bytes == geom.nbytes
+        geom_copy = geom.copy()
+        geom[:] = np.nan                                   # the handle owns its own copy
+        femtc.set_option("host_chunk_mb", 1)
+        try:
+            for rep in range(3):
+                Ur = U * (rep + 1) - rep
+                ref = oracle_run(oracle, op, phi, Ur, geom_copy, P, mode)
+                W = np.full_like(Ur, np.nan)
+                assert K.apply(Ur, W) == 0
+                assert rel_err(W, ref) <= TOL[dt]
+                assert np.array_equal(W, run_host(femtc, op, phi, Ur, geom_copy, P, mode))
+                dU = torch_cuda.from_numpy(Ur).cuda()
+                dW = torch_cuda.full_like(dU, float("nan"))
+                assert K.apply(dU, dW) == 0
+                torch_cuda.cuda.synchronize()
+                assert np.array_equal(dW.cpu().numpy(), W)
+        finally:
+            femtc.set_option("host_chunk_mb", 64)
+    with pytest.raises(RuntimeError):
+        K.apply(U, np.empty_like(U))                       # destroyed by the context manager
+
+
 @pytest.mark.parametrize("op,mode", CASES)
 def test_generic_and_tiled_kernels_agree(femtc, oracle, torch_cuda, op, mode):
     P, dt, nc = 3, "float64", 2048
