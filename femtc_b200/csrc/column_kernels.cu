@@ -482,7 +482,14 @@ mass_column_kernel(const __grid_constant__ TabA<T, N1> B, const T* __restrict__ 
 // issued by lane k.  fp32 records are 24 bytes, so a piece may start / end on an 8-byte boundary:
 // the copy then covers the enclosing 16-byte units and readers skip the leading 8 bytes (`shift`);
 // tiles are whole 16-byte units, so the over-read never leaves the tile's own records.
-template <typename T, int N1, int C, int MODE, int NG>
+//
+// PW = true (producer-warp variant): one extra warp per block requests the geometry for the whole
+// block -- per plane one bulk copy per cell of the tile (n1^2 records, contiguous) into a block-wide
+// ring slot -- and the compute warps only wait on the slot's `full` barrier and arrive on its `empty`
+// barrier.  The per-plane request code (address arithmetic, election loop around the bulk copy) then
+// runs C times per block instead of once per warp, which is what the issue-bound high-degree fp32
+// kernels need (ncu: profiles/r01_ncu_weak_configs_before.txt).
+template <typename T, int N1, int C, int MODE, int NG, bool PW = false>
 struct StiffCol
 {
   using G = ColGeom<T, N1, C>;
@@ -490,22 +497,26 @@ struct StiffCol
   static constexpr int RB = 6 * (int)sizeof(T);                          // record bytes
   static constexpr int MAXP = (32 + G::N2 - 2) / G::N2 + 1;              // pieces a warp can have
   static constexpr bool F32 = sizeof(T) == 4;
-  static constexpr int slot_bytes = up16(32 * RB) + (F32 ? 32 * MAXP + 16 : 0);
+  static constexpr int piece_stride = up16(G::N2 * RB + (F32 ? 8 : 0));  // PW: one cell's plane (+ fp32 skew)
+  static constexpr int slot_bytes = PW ? C * piece_stride : up16(32 * RB) + (F32 ? 32 * MAXP + 16 : 0);
+  static constexpr int ring_bytes = (PW ? 1 : G::NWARPS) * NG * slot_bytes;
+  static constexpr int n_bars = PW ? 1 + 2 * NG : 1 + G::NWARPS * NG;
+  static constexpr int threads = G::NT + (PW ? 32 : 0);
   static constexpr int NE = G::viaC ? 4 : 3;
   static constexpr int off_u = 0;
   static constexpr int off_e = off_u + G::stage_bytes;
   static constexpr int off_g = off_e + NE * G::e_bytes;
-  static constexpr int off_bar = off_g + G::NWARPS * NG * slot_bytes;
-  static constexpr int smem_bytes = off_bar + 8 * (1 + G::NWARPS * NG) + 8;
-  static constexpr int min_blocks = min_blocks_for(G::NT, smem_bytes, sizeof(T) == 8 ? (FULL ? 128 : 104) : (FULL ? 104 : 72));
+  static constexpr int off_bar = off_g + ring_bytes;
+  static constexpr int smem_bytes = off_bar + 8 * n_bars + 8;
+  static constexpr int min_blocks = min_blocks_for(threads, smem_bytes, sizeof(T) == 8 ? (FULL ? 128 : 104) : (FULL ? 104 : 72));
 };
 
-template <typename T, int N1, int C, int MODE, int NG>
-__global__ void __launch_bounds__(ColGeom<T, N1, C>::NT, StiffCol<T, N1, C, MODE, NG>::min_blocks)
+template <typename T, int N1, int C, int MODE, int NG, bool PW>
+__global__ void __launch_bounds__(StiffCol<T, N1, C, MODE, NG, PW>::threads, StiffCol<T, N1, C, MODE, NG, PW>::min_blocks)
 stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restrict__ U, T* __restrict__ W,
                         const T* __restrict__ Gm, long long ntiles)
 {
-  using SC = StiffCol<T, N1, C, MODE, NG>;
+  using SC = StiffCol<T, N1, C, MODE, NG, PW>;
   using G = ColGeom<T, N1, C>;
   using L = typename G::L;
   using PA = typename G::PA;
@@ -524,9 +535,18 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   T* E2 = reinterpret_cast<T*>(smem + SC::off_e + 2 * G::e_bytes);
   T* E3 = reinterpret_cast<T*>(smem + SC::off_e + 3 * G::e_bytes); // only with viaC
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  unsigned char* gRing = smem + SC::off_g + warp * NG * SC::slot_bytes;
+  unsigned char* gRing = smem + SC::off_g + (PW ? 0 : warp * NG * SC::slot_bytes);
   const uint32_t barU = smem_u32(smem + SC::off_bar);
-  const uint32_t barG = barU + 8 + warp * NG * 8;
+  const uint32_t barG = barU + 8 + (PW ? 0 : warp * NG * 8);   // `full` barriers of the ring slots
+  const uint32_t barE = barG + 8 * NG;                            // PW: `empty` barriers
+  // the compute threads' block barrier (the producer warp never takes part in it)
+  auto block_sync = [&]()
+  {
+    if constexpr (PW)
+      asm volatile("bar.sync 1, %0;" ::"n"(G::NT) : "memory");
+    else
+      __syncthreads();
+  };
 
   const int te = min(tid, G::ACTIVE - 1);
   const int c = te / N2, p = te - c * N2;
@@ -547,8 +567,10 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   // as reader: my piece is the one of my (cloned) thread
   const int my_k = c - cFirst;
   const int my_qs = max(q0, c * N2);
-  const int my_par = (c * ND + (my_qs - c * N2)) & 1;         // fp32: parity of the piece's first record
-  const int my_off = up16(RB * (my_qs - q0)) + (SC::F32 ? 32 * my_k : 0) + RB * (te - my_qs);
+  // fp32: parity of the piece's first record; PW: a piece is a whole cell plane
+  const int my_par = PW ? ((c * ND) & 1) : ((c * ND + (my_qs - c * N2)) & 1);
+  const int my_off = PW ? c * SC::piece_stride + RB * p
+                        : up16(RB * (my_qs - q0)) + (SC::F32 ? 32 * my_k : 0) + RB * (te - my_qs);
 
   const long long my_tiles = (long long)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
@@ -566,7 +588,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
 
   auto request_plane = [&](int plane, int slot, const unsigned char* tile_src)
   {
-    if (issuer)
+    if (!PW && issuer)
     {
       const int sh = SC::F32 ? ((is_par + plane * (N2 & 1)) & 1) : 0;
       const uint32_t bytes = sh ? is_bytes1 : is_bytes0;
@@ -581,19 +603,67 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
     mbar_init(barU, 1);
     fence_mbar_init();
   }
-  if (lane == 0)
+  if constexpr (PW)
+  {
+    if (tid == 0)
+    {
+      for (int s = 0; s < NG; ++s)
+      {
+        mbar_init(barG + 8 * s, C);          // one arrive.expect_tx per cell piece
+        mbar_init(barE + 8 * s, G::NWARPS);  // one arrive per compute warp
+      }
+      fence_mbar_init();
+    }
+  }
+  else if (lane == 0)
   {
     for (int s = 0; s < NG; ++s)
       mbar_init(barG + 8 * s, npieces);
     fence_mbar_init();
   }
   __syncthreads();
+  if constexpr (PW)
+  {
+    if (warp == G::NWARPS)
+    {
+      // ---- producer warp: lane k streams the planes of cell k of every tile of this block ------------------
+      if (lane < C)
+      {
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(Gm) +
+                                   ((size_t)blockIdx.x * C + lane) * ND * RB;   // cell `lane`, plane 0
+        const int par0 = SC::F32 ? ((lane * ND) & 1) : 0;                       // tile bases are even record counts
+        const uint32_t dst = smem_u32(gRing) + lane * SC::piece_stride;
+        constexpr uint32_t bytes0 = (uint32_t)up16(N2 * RB), bytes1 = (uint32_t)up16(N2 * RB + 8);
+        int slot = 0;
+        uint32_t epar = 1;                                                      // a fresh barrier passes parity 1
+        for (long long t = 0; t < my_tiles; ++t)
+        {
+#pragma unroll
+          for (int pl = 0; pl < N1; ++pl)
+          {
+            const int sh = SC::F32 ? ((par0 + pl * (N2 & 1)) & 1) : 0;
+            const uint32_t bytes = sh ? bytes1 : bytes0;
+            mbar_wait(barE + 8 * slot, epar);
+            mbar_expect_tx(barG + 8 * slot, bytes);
+            bulk_g2s(dst + slot * SC::slot_bytes, src + pl * (N2 * RB) - 8 * sh, bytes, barG + 8 * slot);
+            if (++slot == NG)
+            {
+              slot = 0;
+              epar ^= 1;
+            }
+          }
+          src += g_stride;
+        }
+      }
+      return;
+    }
+  }
   if (tid == 0 && tile < ntiles)
   {
     mbar_expect_tx(barU, G::tile_bytes);
     bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
   }
-  if (my_tiles > 0)
+  if (!PW && my_tiles > 0)
     for (int s = 0; s < NG; ++s)
       request_plane(s, s, g_tile);
   int c_slot = 0;
@@ -621,7 +691,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       {
         col_load<Nat<N1>, PC>(uS, c * ND + p, y);
         col_store<XCA, PC>(E3, col_base<XCA, PC>(c, hi, lo), y);
-        __syncthreads(); // (0)
+        block_sync(); // (0)
         next_u();
         src = E3, sbase = col_base<XCA, PA>(c, hi, lo), sstride = xstride<XCA, 2>();
       }
@@ -637,7 +707,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
     if constexpr (!G::viaC)
       if (tid == 0)
         bulk_wait_read0(); // the previous tile's W store has finished reading E2
-    __syncthreads(); // (1)
+    block_sync(); // (1)
     if constexpr (!G::viaC)
       next_u();
     // ---- phase B: axis 1 ------------------------------------------------------------------------------------
@@ -653,13 +723,13 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       {
         T ys[N1];
         contract_in(B.a, E1, col_base<XAB, PB>(c, hi, lo), xstride<XAB, 1>(), ys);           // A1 D2 u
-        __syncthreads(); // (1b) E0, E1 are rewritten below
+        block_sync(); // (1b) E0, E1 are rewritten below
         col_store<XBC, PB>(E0, col_base<XBC, PB>(c, hi, lo), ya);
         col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), yd);
         col_store<XBC, PB>(E2, col_base<XBC, PB>(c, hi, lo), ys);
       }
     }
-    __syncthreads(); // (2)
+    block_sync(); // (2)
     // ---- phase C: axis 0 forward, geometry, axis 0 backward -- fused plane by plane ---------------------------
     // For plane i0:  w0 = D(i0,:) ta, w1 = A(i0,:) td, w2 = A(i0,:) ta   [REF_EXACT: stiffness.hpp:68-77]
     //                                                  w2 = A(i0,:) sa   [FULL]
@@ -736,7 +806,12 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         // REF_EXACT: only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
         col_axpy(B.a, i0, f2, h2);                              // A0 f2
         __syncwarp(); // every lane is done with this slot: request the chunk NG ahead into it
-        if (i0 + NG < N1)
+        if constexpr (PW)
+        {
+          if (lane == 0)
+            mbar_arrive(barE + 8 * c_slot);
+        }
+        else if (i0 + NG < N1)
           request_plane(i0 + NG, c_slot, g_tile);
         else if (tn < ntiles)
           request_plane(i0 + NG - N1, c_slot, g_tile + g_stride);
@@ -750,14 +825,14 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h2);
       else
       {
-        __syncthreads(); // (2b) E0..E2 were read by this phase
+        block_sync(); // (2b) E0..E2 were read by this phase
         col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h0);
         col_store<XBC, PC>(E1, col_base<XBC, PC>(c, hi, lo), h1);
         col_store<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), h2);
       }
     }
     g_tile += g_stride;
-    __syncthreads(); // (3)
+    block_sync(); // (3)
     // ---- phase B': back along axis 1 --------------------------------------------------------------------------
     {
       T m[N1];
@@ -769,12 +844,12 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         T n[N1];
         contract_in_add(B.d, E1, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), m);        // + D1 A0 f1
         contract_in(B.a, E2, col_base<XBC, PB>(c, hi, lo), xstride<XBC, 1>(), n);            // A1 A0 f2
-        __syncthreads(); // (3b)
+        block_sync(); // (3b)
         col_store<XAB, PB>(E0, col_base<XAB, PB>(c, hi, lo), m);
         col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), n);
       }
     }
-    __syncthreads(); // (4)
+    block_sync(); // (4)
     // ---- phase A': back along axis 2, W ---------------------------------------------------------------------------
     {
       T out[N1];
@@ -788,7 +863,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       if constexpr (G::viaC)
       {
         col_store<XCA, PA>(E2, col_base<XCA, PA>(c, hi, lo), out);
-        __syncthreads(); // (5)
+        block_sync(); // (5)
         col_load<XCA, PC>(E2, col_base<XCA, PC>(c, hi, lo), out);
         if (tid < G::ACTIVE)
         {
@@ -802,7 +877,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       {
         col_store<Nat<N1>, PA>(E2, col_base<Nat<N1>, PA>(c, hi, lo), out);
         fence_proxy_async();
-        __syncthreads(); // (5)
+        block_sync(); // (5)
         if (tid == 0)
         {
           bulk_s2g(W + (size_t)tile * C * ND, smem_u32(E2), G::tile_bytes);
@@ -865,10 +940,10 @@ long long run_mass_col(const MassArgs<T>& a)
   return ntiles * C;
 }
 
-template <typename T, int N1, int C, int MODE, int NG>
+template <typename T, int N1, int C, int MODE, int NG, bool PW>
 long long run_stiff_col(const StiffnessArgs<T>& a)
 {
-  using SC = StiffCol<T, N1, C, MODE, NG>;
+  using SC = StiffCol<T, N1, C, MODE, NG, PW>;
   using G = ColGeom<T, N1, C>;
   const long long ntiles = (long long)(a.num_cells / C);
   if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.G))
@@ -878,24 +953,42 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
   fill_table<T, N1>(B.d, a.D_host, false);
   fill_table<T, N1>(B.at, a.A_host, true);
   fill_table<T, N1>(B.dt, a.D_host, true);
-  auto kernel = stiffness_column_kernel<T, N1, C, MODE, NG>;
+  auto kernel = stiffness_column_kernel<T, N1, C, MODE, NG, PW>;
   int bps = 0;
-  int rc = plan_blocks(kernel, G::NT, SC::smem_bytes, bps);
+  int rc = plan_blocks(kernel, SC::threads, SC::smem_bytes, bps);
   if (rc)
     return -rc;
   const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
-  kernel<<<grid, G::NT, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
+  kernel<<<grid, SC::threads, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
   count_launch();
   if (cudaGetLastError() != cudaSuccess)
     return -FEMTC_ERR_CUDA;
   return ntiles * C;
 }
 
+// Geometry transport per shape: producer warp (PW) where measured faster (profiles/r01_ab_producer_warp.txt:
+// REF_EXACT fp32 n1 = 6..8 +1..3 points, fp64 n1 = 6 85 -> 91 %; it loses at n1 = 9 and in FULL mode, where the
+// block-wide ring couples the warps).  variant 3 / 4 force PW on / off.
+template <typename T, int N1>
+constexpr bool default_pw()
+{
+  return sizeof(T) == 4 ? (N1 >= 6 && N1 <= 8) : N1 == 6;
+}
 template <typename T, int N1, int C, int NG>
 long long run_stiff_col_mode(const StiffnessArgs<T>& a)
 {
-  return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG>(a)
-                                        : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG>(a);
+  const long long v = opt_variant();
+  bool pw = default_pw<T, N1>() && a.mode == FEMTC_STIFFNESS_REF_EXACT;
+  if (v == 3) pw = true;
+  if (v == 4) pw = false;
+  if constexpr (N1 >= 6)
+  {
+    if (pw)
+      return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG + 1, true>(a)
+                                            : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG + 1, true>(a);
+  }
+  return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG, false>(a)
+                                        : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG, false>(a);
 }
 
 } // namespace

@@ -438,6 +438,29 @@ def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, vari
         femtc.set_option("variant", 0)
 
 
+@pytest.mark.parametrize("variant", (3, 4))   # geometry by a producer warp / by warp-private rings
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", (5, 6, 7, 8))
+@pytest.mark.parametrize("mode", (0, 1))
+def test_column_geometry_transport_variants_parity(femtc, oracle, torch_cuda, mode, P, dt, variant):
+    """Both geometry transports of the column stiffness kernels, many tiles per block (ring wrap-around,
+    tile hand-over) plus a ragged tail, bit-identical to each other and within tolerance of the oracle."""
+    nc = {5: 148 * 7 * 9 + 5, 6: 148 * 4 * 9 + 3, 7: 148 * 2 * 13 + 1, 8: 148 * 4 * 7 + 3}[P]
+    femtc.set_option("tc", 0)
+    out = {}
+    try:
+        phi, U, geom = splitmix(oracle, "stiffness", P, nc, dt, seed=40 + P, centred=True)
+        ref = oracle_run(oracle, "stiffness", phi, U, geom, P, mode)
+        for v in (variant, 0):
+            femtc.set_option("variant", v)
+            out[v] = run_device(femtc, torch_cuda, "stiffness", phi, U, geom, P, mode)
+            assert rel_err(out[v], ref) <= TOL[dt], (mode, P, dt, v)
+        assert np.array_equal(out[variant], out[0])
+    finally:
+        femtc.set_option("variant", 0)
+        femtc.set_option("tc", -1)
+
+
 def test_tensor_core_large_batch_matches_column_kernel(femtc, torch_cuda):
     """Same inputs through the DMMA family and the FMA column family at a size with many blocks per SM and
     a ring that wraps: the two must agree to rounding (1e-13) on every one of the 20 000 cells."""
