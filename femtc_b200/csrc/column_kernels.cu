@@ -578,7 +578,7 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   // side, so while plane i0 of a tile is consumed the plane to request is i0 + NG of the same tile, or
   // i0 + NG - N1 of the block's next tile -- a compile-time distinction wherever the plane loop is
   // unrolled.  Only (slot, parity) and one byte pointer per tile are carried.
-  static_assert(NG <= N1, "the geometry ring may run at most one tile ahead");
+  static_assert(PW || NG <= N1, "the warp-private geometry ring may run at most one tile ahead");
   const unsigned char* g_tile = reinterpret_cast<const unsigned char*>(Gm) +
                                 ((size_t)blockIdx.x * C * ND + is_rec) * RB;   // my piece, plane 0, current tile
   const size_t g_stride = (size_t)gridDim.x * C * ND * RB;                      // to the block's next tile
@@ -966,29 +966,45 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
   return ntiles * C;
 }
 
-// Geometry transport per shape: producer warp (PW) where measured faster (profiles/r01_ab_producer_warp.txt:
-// REF_EXACT fp32 n1 = 6..8 +1..3 points, fp64 n1 = 6 85 -> 91 %; it loses at n1 = 9 and in FULL mode, where the
-// block-wide ring couples the warps).  variant 3 / 4 force PW on / off.
+// Geometry transport per shape (REF_EXACT): depth of the block-wide producer-warp ring, 0 = warp-private rings.
+// Measured (profiles/r01_ab_producer_warp.txt, r01_ab_producer_warp_depth.txt; % of measured HBM, 1 M cells):
+//   fp32 n1=6  84 (private) -> 85 (3) -> 96 (5) -> 101 (8)      fp32 n1=7  69 -> 70 -> 78 -> 80
+//   fp32 n1=8  90 -> 91..92 (3) -> 88 (5) -> 66 (8)              fp32 n1=9  63 (private) vs 58..60: stays private
+//   fp64 n1=6  85 -> 90..91 (3) -> 70 (5)                        fp64 n1=7..9 and FULL mode: private is faster
+// variant 3 / 4 force the depth-3 ring / the private rings, 5 / 6 the depth-5 / depth-8 ring (development).
 template <typename T, int N1>
-constexpr bool default_pw()
+constexpr int default_pw_depth()
 {
-  return sizeof(T) == 4 ? (N1 >= 6 && N1 <= 8) : N1 == 6;
+  if (sizeof(T) == 4)
+    return N1 == 6 || N1 == 7 ? 8 : (N1 == 8 ? 3 : 0);
+  return N1 == 6 ? 3 : 0;
 }
 template <typename T, int N1, int C, int NG>
 long long run_stiff_col_mode(const StiffnessArgs<T>& a)
 {
-  const long long v = opt_variant();
-  bool pw = default_pw<T, N1>() && a.mode == FEMTC_STIFFNESS_REF_EXACT;
-  if (v == 3) pw = true;
-  if (v == 4) pw = false;
+  if (a.mode == FEMTC_STIFFNESS_FULL)
+  {
+    if constexpr (N1 >= 6)
+      if (opt_variant() == 3)
+        return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, 3, true>(a);
+    return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG, false>(a);
+  }
   if constexpr (N1 >= 6)
   {
-    if (pw)
-      return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG + 1, true>(a)
-                                            : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG + 1, true>(a);
+    int depth = default_pw_depth<T, N1>();
+    switch (opt_variant())
+    {
+    case 3: depth = 3; break;
+    case 4: depth = 0; break;
+    case 5: depth = 5; break;
+    case 6: depth = 8; break;
+    default: break;
+    }
+    if (depth == 3) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 3, true>(a);
+    if (depth == 5) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 5, true>(a);
+    if (depth == 8) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 8, true>(a);
   }
-  return a.mode == FEMTC_STIFFNESS_FULL ? run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG, false>(a)
-                                        : run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG, false>(a);
+  return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG, false>(a);
 }
 
 } // namespace

