@@ -970,14 +970,22 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
 // Measured (profiles/r01_ab_producer_warp.txt, r01_ab_producer_warp_depth.txt; % of measured HBM, 1 M cells):
 //   fp32 n1=6  84 (private) -> 85 (3) -> 96 (5) -> 101 (8)      fp32 n1=7  69 -> 70 -> 78 -> 80
 //   fp32 n1=8  90 -> 91..92 (3) -> 88 (5) -> 66 (8)              fp32 n1=9  63 (private) vs 58..60: stays private
-//   fp64 n1=6  85 -> 90..91 (3) -> 70 (5)                        fp64 n1=7..9 and FULL mode: private is faster
-// variant 3 / 4 force the depth-3 ring / the private rings, 5 / 6 the depth-5 / depth-8 ring (development).
+//   fp64 n1=6  85 -> 90..91 (3) -> 70 (5), private depth 4: 94   fp64 n1=7..9 and FULL mode: private is faster
+// variant 3 / 4 force the depth-3 ring / the depth-2 private rings, 5 / 6 the depth-5 / depth-8 ring,
+// 7 / 8 private rings of depth 4 / 6 (development).
 template <typename T, int N1>
 constexpr int default_pw_depth()
 {
   if (sizeof(T) == 4)
     return N1 == 6 || N1 == 7 ? 8 : (N1 == 8 ? 3 : 0);
-  return N1 == 6 ? 3 : 0;
+  return 0;
+}
+// depth of the warp-private rings where those serve (fp64 n1 = 6: 85 % at 2, 94 % at 4 -- better than the
+// block-wide ring's 91 %; deeper rings cost a resident block everywhere else: profiles/r01_ab_private_ring_depth.txt)
+template <typename T, int N1>
+constexpr int default_private_depth()
+{
+  return sizeof(T) == 8 && N1 == 6 ? 4 : 2;
 }
 template <typename T, int N1, int C, int NG>
 long long run_stiff_col_mode(const StiffnessArgs<T>& a)
@@ -1000,10 +1008,15 @@ long long run_stiff_col_mode(const StiffnessArgs<T>& a)
     case 6: depth = 8; break;
     default: break;
     }
+    if (opt_variant() == 7) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 4, false>(a); // deeper private rings
+    if (opt_variant() == 8) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 6, false>(a);
     if (depth == 3) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 3, true>(a);
     if (depth == 5) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 5, true>(a);
     if (depth == 8) return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 8, true>(a);
   }
+  if constexpr (N1 >= 6 && default_private_depth<T, N1>() == 4)
+    if (opt_variant() != 4)
+      return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, 4, false>(a);
   return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_REF_EXACT, NG, false>(a);
 }
 
