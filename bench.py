@@ -489,8 +489,19 @@ def run_ours(a, rank: int, local_rank: int, world: int):
         dist.destroy_process_group()
 
 
+def _keep_stdout_for_the_json_line():
+    """The contract is ONE JSON line on stdout.  Libraries underneath (NCCL prints its version banner on
+    stdout when NCCL_DEBUG=VERSION is set on the box) must not add to it: from here on file descriptor 1
+    points at stderr, and sys.stdout keeps a private copy of the original stdout for our own print."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real
+
+
 def main():
     a = parse_args()
+    _keep_stdout_for_the_json_line()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -501,7 +512,7 @@ def main():
         # convenience: `python bench.py --gpus N` without torchrun re-launches itself under it
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", str(Path(__file__).resolve())] + sys.argv[1:]
-        raise SystemExit(subprocess.call(cmd))
+        raise SystemExit(subprocess.call(cmd, stdout=sys.stdout))  # the child inherits the real stdout
     if a.total_cells:
         run_strong(a, rank, local_rank, world)
     else:
