@@ -259,6 +259,172 @@ __device__ __forceinline__ void col_axpy(const T (&M)[N1 * tab_ld<N1>()], int p,
     y[i] = fma_t(m[i], f, y[i]);
 }
 
+// ---- two cells per thread -------------------------------------------------------------------------------
+// An fp64 FMA cannot take a constant-bank operand: every DFMA of the contractions above is paired with the
+// LDCU that brings its matrix entry into a uniform register (ncu, fp64 mass n1 = 9: LDCU 38 % = DFMA 37 % of
+// the executed instructions).  A thread that owns the same column of TWO cells uses each fetched entry
+// twice.  `delta` = distance between the two cells' columns in the buffer.
+template <int CNT, typename T, int N1>
+__device__ __forceinline__ void contract_in_trip_x2(const T* M, int off, const T* ptr, int delta, int stride, T (&y0)[N1],
+                                                    T (&y1)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  T xa[CNT], xb[CNT];
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+  {
+    xa[u] = ptr[u * stride];
+    xb[u] = ptr[u * stride + delta];
+  }
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+  {
+    T m[N1];
+    tab_run<T, N1>(M, off + u * LD, m);
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+    {
+      y0[i] = fma_t(m[i], xa[u], y0[i]);
+      y1[i] = fma_t(m[i], xb[u], y1[i]);
+    }
+  }
+}
+// y0[i] = sum_p A(i,p) buf[base + p*stride],  y1[i] = sum_p A(i,p) buf[base + delta + p*stride]
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in_x2(const T (&M)[N1 * tab_ld<N1>()], const T* buf, int base, int delta, int stride,
+                                               T (&y0)[N1], T (&y1)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  constexpr int U = Roll<T, N1>::in;
+  constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
+#pragma unroll
+  for (int i = 0; i < N1; ++i)
+    y0[i] = y1[i] = T(0);
+  const T* ptr = buf + base;
+  if constexpr (TRIPS == 1)
+    contract_in_trip_x2<U>(M, 0, ptr, delta, stride, y0, y1);
+  else
+  {
+    int off = 0;
+#pragma unroll 1
+    for (int t = 0; t < TRIPS; ++t)
+    {
+      contract_in_trip_x2<U>(M, off, ptr, delta, stride, y0, y1);
+      ptr += U * stride;
+      off += U * LD;
+    }
+  }
+  if constexpr (REM > 0 && TRIPS != 1)
+    contract_in_trip_x2<REM>(M, TRIPS * U * LD, ptr, delta, stride, y0, y1);
+}
+// two matrices applied to the same column of two cells (four accumulator columns per thread)
+template <int CNT, typename T, int N1>
+__device__ __forceinline__ void contract_in2_trip_x2(const T* Ma, const T* Mb, int off, const T* ptr, int delta, int stride,
+                                                     T (&ya0)[N1], T (&yb0)[N1], T (&ya1)[N1], T (&yb1)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  T xa[CNT], xb[CNT];
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+  {
+    xa[u] = ptr[u * stride];
+    xb[u] = ptr[u * stride + delta];
+  }
+#pragma unroll
+  for (int u = 0; u < CNT; ++u)
+  {
+    T m[N1];
+    tab_run<T, N1>(Ma, off + u * LD, m);
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+    {
+      ya0[i] = fma_t(m[i], xa[u], ya0[i]);
+      ya1[i] = fma_t(m[i], xb[u], ya1[i]);
+    }
+    tab_run<T, N1>(Mb, off + u * LD, m);
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+    {
+      yb0[i] = fma_t(m[i], xa[u], yb0[i]);
+      yb1[i] = fma_t(m[i], xb[u], yb1[i]);
+    }
+  }
+}
+template <typename T, int N1>
+__device__ __forceinline__ void contract_in2_x2(const T (&Ma)[N1 * tab_ld<N1>()], const T (&Mb)[N1 * tab_ld<N1>()], const T* buf,
+                                                int base, int delta, int stride, T (&ya0)[N1], T (&yb0)[N1], T (&ya1)[N1],
+                                                T (&yb1)[N1])
+{
+  constexpr int LD = tab_ld<N1>();
+  constexpr int U = Roll<T, N1>::in;
+  constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
+#pragma unroll
+  for (int i = 0; i < N1; ++i)
+    ya0[i] = yb0[i] = ya1[i] = yb1[i] = T(0);
+  const T* ptr = buf + base;
+  if constexpr (TRIPS == 1)
+    contract_in2_trip_x2<U>(Ma, Mb, 0, ptr, delta, stride, ya0, yb0, ya1, yb1);
+  else
+  {
+    int off = 0;
+#pragma unroll 1
+    for (int t = 0; t < TRIPS; ++t)
+    {
+      contract_in2_trip_x2<U>(Ma, Mb, off, ptr, delta, stride, ya0, yb0, ya1, yb1);
+      ptr += U * stride;
+      off += U * LD;
+    }
+  }
+  if constexpr (REM > 0 && TRIPS != 1)
+    contract_in2_trip_x2<REM>(Ma, Mb, TRIPS * U * LD, ptr, delta, stride, ya0, yb0, ya1, yb1);
+}
+// buf[base + i*stride] = sum_p A(i,p) z0[p],  buf[base + delta + i*stride] = sum_p A(i,p) z1[p]   (MT transposed table)
+template <typename T, int N1>
+__device__ __forceinline__ void row_dot_x2(const T* MT, int off, const T (&z0)[N1], const T (&z1)[N1], T& r0, T& r1)
+{
+  T m[N1];
+  tab_run<T, N1>(MT, off, m);
+  T a0 = m[0] * z0[0], a1 = m[0] * z1[0];
+#pragma unroll
+  for (int p = 1; p < N1; ++p)
+  {
+    a0 = fma_t(m[p], z0[p], a0);
+    a1 = fma_t(m[p], z1[p], a1);
+  }
+  r0 = a0, r1 = a1;
+}
+template <typename T, int N1>
+__device__ __forceinline__ void contract_out_x2(const T (&MT)[N1 * tab_ld<N1>()], const T (&z0)[N1], const T (&z1)[N1], T* buf,
+                                                int base, int delta, int stride)
+{
+  constexpr int LD = tab_ld<N1>();
+  constexpr int U = Roll<T, N1>::in;
+  constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
+  T* ptr = buf + base;
+  if constexpr (TRIPS == 1)
+  {
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      row_dot_x2<T, N1>(MT, i * LD, z0, z1, ptr[i * stride], ptr[i * stride + delta]);
+  }
+  else
+  {
+    int off = 0;
+#pragma unroll 1
+    for (int t = 0; t < TRIPS; ++t)
+    {
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        row_dot_x2<T, N1>(MT, off + u * LD, z0, z1, ptr[u * stride], ptr[u * stride + delta]);
+      ptr += U * stride;
+      off += U * LD;
+    }
+#pragma unroll
+    for (int u = 0; u < REM; ++u)
+      row_dot_x2<T, N1>(MT, (TRIPS * U + u) * LD, z0, z1, ptr[u * stride], ptr[u * stride + delta]);
+  }
+}
+
 template <class X, int AXIS>
 constexpr int xstride()
 {
@@ -472,6 +638,157 @@ mass_column_kernel(const __grid_constant__ TabA<T, N1> B, const T* __restrict__ 
 #pragma unroll
       for (int r = 0; r < N1; ++r)
         w[r * N2] = x[r];
+    }
+  }
+}
+
+// ---- mass, two cells per thread (fp64 high degree) -----------------------------------------------------------
+// Same phases, staging and exchange layouts as mass_column_kernel on a tile of C cells, but only C/2 cells'
+// worth of threads: thread (c, hi, lo) owns that column in cells c and c + C/2 and shares every matrix fetch
+// between the two (contract_in_x2 / contract_out_x2).
+template <typename T, int N1, int C>
+struct MassCol2
+{
+  static_assert(C % 2 == 0, "two cells per thread");
+  using G = ColGeom<T, N1, C>;      // memory geometry: the whole tile
+  using M1 = MassCol<T, N1, C>;
+  static constexpr int ACTIVE = (C / 2) * N1 * N1;  // thread geometry: half of the tile's cells
+  static constexpr int NT = (ACTIVE + 31) & ~31;
+  static constexpr int smem_bytes = M1::smem_bytes;
+  static constexpr int min_blocks = min_blocks_for(NT, smem_bytes, 96);
+};
+
+template <typename T, int N1, int C>
+__global__ void __launch_bounds__(MassCol2<T, N1, C>::NT, MassCol2<T, N1, C>::min_blocks)
+mass_column2_kernel(const __grid_constant__ TabA<T, N1> B, const T* __restrict__ U, T* __restrict__ W,
+                    const T* __restrict__ J, long long ntiles)
+{
+  using MC = MassCol<T, N1, C>;
+  using G = ColGeom<T, N1, C>;
+  using H = MassCol2<T, N1, C>;
+  using L = typename G::L;
+  using PA = typename G::PA;
+  using PB = typename G::PB;
+  using PC = typename G::PC;
+  using XBC = typename L::XBC;
+  using XAB = typename L::XAB;
+  using XCA = typename L::XCA;
+  constexpr int ND = G::ND, N2 = G::N2, CH = C / 2;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  T* uS = reinterpret_cast<T*>(smem + MC::off_u);
+  T* jS = reinterpret_cast<T*>(smem + MC::off_j);
+  T* E0 = reinterpret_cast<T*>(smem + MC::off_e);
+  T* E1 = reinterpret_cast<T*>(smem + MC::off_e + G::e_bytes);
+  T* E2 = reinterpret_cast<T*>(smem + MC::off_e + 2 * G::e_bytes); // only with viaC
+  const uint32_t barU = smem_u32(smem + MC::off_bar), barJ = barU + 8;
+
+  const int tid = threadIdx.x;
+  const int te = min(tid, H::ACTIVE - 1); // idle lanes clone the last active thread
+  const int c = te / N2, p = te - c * N2;
+  const int hi = p / N1, lo = p - hi * N1;
+
+  long long tile = blockIdx.x;
+  if (tid == 0)
+  {
+    mbar_init(barU, 1);
+    mbar_init(barJ, 1);
+    fence_mbar_init();
+    if (tile < ntiles)
+    {
+      mbar_expect_tx(barU, G::tile_bytes);
+      bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
+      mbar_expect_tx(barJ, G::tile_bytes);
+      bulk_g2s(smem_u32(jS), J + (size_t)tile * C * ND, G::tile_bytes, barJ);
+    }
+  }
+  __syncthreads();
+
+  uint32_t phase = 0;
+  for (; tile < ntiles; tile += gridDim.x, phase ^= 1)
+  {
+    const long long tn = tile + gridDim.x;
+    T x0[N1], x1[N1];
+    // ---- phase C: forward along axis 0 (mass.hpp:36) -------------------------------------------------
+    mbar_wait(barU, phase);
+    if constexpr (G::viaC)
+    {
+      T d[N1];
+      mbar_wait(barJ, phase);
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+      {
+        col_load<Nat<N1>, PC>(jS, (c + r * CH) * ND + p, d);
+        col_store<XCA, PC>(E2, col_base<XCA, PC>(c + r * CH, hi, lo), d);
+      }
+    }
+    contract_in_x2(B.a, uS, c * ND + p, CH * ND, N2, x0, x1);
+    col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), x0);
+    col_store<XBC, PC>(E0, col_base<XBC, PC>(c + CH, hi, lo), x1);
+    __syncthreads(); // (1) staging consumed, E0 complete
+    if (tid == 0 && tn < ntiles)
+    {
+      mbar_expect_tx(barU, G::tile_bytes);
+      bulk_g2s(smem_u32(uS), U + (size_t)tn * C * ND, G::tile_bytes, barU);
+      if constexpr (G::viaC)
+      {
+        mbar_expect_tx(barJ, G::tile_bytes);
+        bulk_g2s(smem_u32(jS), J + (size_t)tn * C * ND, G::tile_bytes, barJ);
+      }
+    }
+    // ---- phase B: axis 1 (mass.hpp:37) ------------------------------------------------------------------
+    contract_in_x2(B.a, E0, col_base<XBC, PB>(c, hi, lo), CH * XBC::Sc, xstride<XBC, 1>(), x0, x1);
+    col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), x0);
+    col_store<XAB, PB>(E1, col_base<XAB, PB>(c + CH, hi, lo), x1);
+    __syncthreads(); // (2)
+    // ---- phase A: axis 2, quadrature scaling (mass.hpp:38-41), back along axis 2 (mass.hpp:45) ----------
+    contract_in_x2(B.a, E1, col_base<XAB, PA>(c, hi, lo), CH * XAB::Sc, xstride<XAB, 2>(), x0, x1);
+    {
+      T d0[N1], d1[N1];
+      if constexpr (G::viaC)
+      {
+        col_load<XCA, PA>(E2, col_base<XCA, PA>(c, hi, lo), d0);
+        col_load<XCA, PA>(E2, col_base<XCA, PA>(c + CH, hi, lo), d1);
+      }
+      else
+      {
+        mbar_wait(barJ, phase);
+        col_load<Nat<N1>, PA>(jS, col_base<Nat<N1>, PA>(c, hi, lo), d0);
+        col_load<Nat<N1>, PA>(jS, col_base<Nat<N1>, PA>(c + CH, hi, lo), d1);
+      }
+#pragma unroll
+      for (int r = 0; r < N1; ++r)
+      {
+        x0[r] = x0[r] * d0[r];
+        x1[r] = x1[r] * d1[r];
+      }
+    }
+    contract_out_x2(B.at, x0, x1, E0, col_base<XAB, PA>(c, hi, lo), CH * XAB::Sc, xstride<XAB, 2>());
+    __syncthreads(); // (3)
+    if constexpr (!G::viaC)
+    {
+      if (tid == 0 && tn < ntiles)
+      {
+        mbar_expect_tx(barJ, G::tile_bytes);
+        bulk_g2s(smem_u32(jS), J + (size_t)tn * C * ND, G::tile_bytes, barJ);
+      }
+    }
+    // ---- phase B': back along axis 1 (mass.hpp:46) ---------------------------------------------------
+    contract_in_x2(B.a, E0, col_base<XAB, PB>(c, hi, lo), CH * XAB::Sc, xstride<XAB, 1>(), x0, x1);
+    col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), x0);
+    col_store<XBC, PB>(E1, col_base<XBC, PB>(c + CH, hi, lo), x1);
+    __syncthreads(); // (4)
+    // ---- phase C': back along axis 0 (mass.hpp:47), coalesced store of W ---------------------------------
+    contract_in_x2(B.a, E1, col_base<XBC, PC>(c, hi, lo), CH * XBC::Sc, xstride<XBC, 0>(), x0, x1);
+    if (tid < H::ACTIVE)
+    {
+      T* w = W + (size_t)tile * C * ND + c * ND + p;
+#pragma unroll
+      for (int r = 0; r < N1; ++r)
+      {
+        w[r * N2] = x0[r];
+        w[r * N2 + CH * ND] = x1[r];
+      }
     }
   }
 }
@@ -940,6 +1257,30 @@ long long run_mass_col(const MassArgs<T>& a)
   return ntiles * C;
 }
 
+template <typename T, int N1, int C>
+long long run_mass_col2(const MassArgs<T>& a)
+{
+  using MC = MassCol2<T, N1, C>;
+  using H = MassCol2<T, N1, C>;
+  const long long ntiles = (long long)(a.num_cells / C);
+  if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.detJ))
+    return 0;
+  TabA<T, N1> B;
+  fill_table<T, N1>(B.a, a.phi_host, false);
+  fill_table<T, N1>(B.at, a.phi_host, true);
+  auto kernel = mass_column2_kernel<T, N1, C>;
+  int bps = 0;
+  int rc = plan_blocks(kernel, H::NT, MC::smem_bytes, bps);
+  if (rc)
+    return -rc;
+  const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
+  kernel<<<grid, H::NT, MC::smem_bytes, a.stream>>>(B, a.U, a.W, a.detJ, ntiles);
+  count_launch();
+  if (cudaGetLastError() != cudaSuccess)
+    return -FEMTC_ERR_CUDA;
+  return ntiles * C;
+}
+
 template <typename T, int N1, int C, int MODE, int NG, bool PW>
 long long run_stiff_col(const StiffnessArgs<T>& a)
 {
@@ -1027,6 +1368,39 @@ template <typename T>
 long long launch_mass_column(const MassArgs<T>& a)
 {
   const int n1 = a.degree + 1;
+  {
+    // Two cells per thread.  Measured (profiles/r01_ab_mass_two_cells.txt, % of measured HBM, one -> two cells):
+    //   fp64 n1 = 6: 78 -> 84 (tile of 14), n1 = 7: 58..64 -> 68, n1 = 9: 47 -> 57; n1 = 8 stays on DMMA (71).
+    // variant 10 / 11 force it with the one-cell kernel's tile / twice that tile, variant 12 forces one cell.
+    const long long v = opt_variant();
+    constexpr bool F64 = sizeof(T) == 8;
+    int two = 0; // 0 = one cell per thread, 1 = tile as the one-cell kernel, 2 = twice that
+    if (F64)
+      two = n1 == 6 ? 2 : (n1 == 7 || n1 == 9 ? 1 : 0);
+    else
+      two = n1 == 8 ? 1 : (n1 == 9 ? 2 : 0); // fp32: n1 = 8 63 -> 73, n1 = 9 57 -> 60; n1 = 6, 7 lose or tie
+    if (v == 10) two = 1;
+    if (v == 11) two = 2;
+    if (v == 12) two = 0;
+    if (two == 1)
+      switch (n1)
+      {
+      case 6: return run_mass_col2<T, 6, 8>(a);
+      case 7: return run_mass_col2<T, 7, 4>(a);
+      case 8: return run_mass_col2<T, 8, 2>(a);
+      case 9: return run_mass_col2<T, 9, F64 ? 2 : 4>(a);
+      default: break;
+      }
+    if (two == 2)
+      switch (n1)
+      {
+      case 6: return run_mass_col2<T, 6, F64 ? 14 : 16>(a);
+      case 7: return run_mass_col2<T, 7, 8>(a);
+      case 8: return run_mass_col2<T, 8, 4>(a);
+      case 9: return run_mass_col2<T, 9, F64 ? 4 : 8>(a);
+      default: break;
+      }
+  }
   switch (n1)
   {
   case 6: return run_mass_col<T, 6, default_cells<T, 6>()>(a);

@@ -462,6 +462,29 @@ def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, vari
         femtc.set_option("variant", 0)
 
 
+@pytest.mark.parametrize("variant", (10, 11))   # two cells per thread, tile = 1x / 2x the one-cell kernel's
+@pytest.mark.parametrize("P", (5, 6, 7, 8))
+def test_mass_two_cells_per_thread_parity(femtc, oracle, torch_cuda, P, variant):
+    """fp64 mass column kernel with two cells per thread: within tolerance of the oracle everywhere and
+    bit-identical to the one-cell kernel (same summation order) on the cells both serve from whole tiles
+    (the ragged tail goes to the generic kernel, whose split point depends on the tile size)."""
+    nc = {5: 148 * 14 * 5 + 9, 6: 148 * 8 * 5 + 5, 7: 148 * 4 * 5 + 3, 8: 148 * 4 * 5 + 1}[P]
+    femtc.set_option("tc", 0)
+    out = {}
+    try:
+        phi, U, geom = splitmix(oracle, "mass", P, nc, "float64", seed=60 + P, centred=True)
+        ref = oracle_run(oracle, "mass", phi, U, geom, P)
+        for v in (variant, 12):                              # 12: one cell per thread
+            femtc.set_option("variant", v)
+            out[v] = run_device(femtc, torch_cuda, "mass", phi, U, geom, P)
+            assert rel_err(out[v], ref) <= TOL["float64"], (P, v)
+        whole = (nc // 56) * 56 * (P + 1) ** 3               # 56 = lcm of every tile size involved
+        assert np.array_equal(out[variant][:whole], out[12][:whole])
+    finally:
+        femtc.set_option("variant", 0)
+        femtc.set_option("tc", -1)
+
+
 @pytest.mark.parametrize("variant", (3, 4, 5, 6))   # geometry by a producer warp (ring depth 3, 5, 8) / by warp-private rings
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("P", (5, 6, 7, 8))
