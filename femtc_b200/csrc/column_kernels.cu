@@ -1208,6 +1208,240 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       bulk_wait_read0();
 }
 
+// ---- stiffness REF_EXACT, two cells per thread -------------------------------------------------------------
+// Same phases, exchange layouts and results as stiffness_column_kernel<.., REF_EXACT, .., PW = true> on a tile of
+// C cells, with C/2 cells' worth of compute threads: thread (c, hi, lo) owns that column in cells c and c + C/2
+// and shares every matrix fetch between the two.  Geometry arrives through the block-wide producer-warp ring
+// (a piece = one cell's plane, so the second cell is one constant offset away).  n1 without the viaC detour only.
+template <typename T, int N1, int C, int NG>
+struct StiffCol2
+{
+  static_assert(C % 2 == 0, "two cells per thread");
+  using G = ColGeom<T, N1, C>;
+  static_assert(!G::viaC, "shapes that stage phase A through a C-order exchange are not served");
+  static constexpr bool F32 = sizeof(T) == 4;
+  static constexpr int RB = 6 * (int)sizeof(T);
+  static constexpr int CH = C / 2;
+  static constexpr int ACTIVE = CH * G::N2;
+  static constexpr int NT = (ACTIVE + 31) & ~31;
+  static constexpr int NWARPS = NT / 32;
+  static constexpr int threads = NT + 32;
+  static constexpr int piece_stride = up16(G::N2 * RB + (F32 ? 8 : 0));
+  static constexpr int slot_bytes = C * piece_stride;
+  static constexpr int off_u = 0;
+  static constexpr int off_e = off_u + G::stage_bytes;
+  static constexpr int off_g = off_e + 3 * G::e_bytes;
+  static constexpr int off_bar = off_g + NG * slot_bytes;
+  static constexpr int smem_bytes = off_bar + 8 * (1 + 2 * NG) + 8;
+  static constexpr int min_blocks = min_blocks_for(threads, smem_bytes, F32 ? 112 : 168);
+};
+
+template <typename T, int N1, int C, int NG>
+__global__ void __launch_bounds__(StiffCol2<T, N1, C, NG>::threads, StiffCol2<T, N1, C, NG>::min_blocks)
+stiffness_column2_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restrict__ U, T* __restrict__ W,
+                         const T* __restrict__ Gm, long long ntiles)
+{
+  using SC = StiffCol2<T, N1, C, NG>;
+  using G = ColGeom<T, N1, C>;
+  using L = typename G::L;
+  using PA = typename G::PA;
+  using PB = typename G::PB;
+  using PC = typename G::PC;
+  using XBC = typename L::XBC;
+  using XAB = typename L::XAB;
+  constexpr int ND = G::ND, N2 = G::N2, RB = SC::RB, CH = SC::CH, LD = tab_ld<N1>();
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  T* uS = reinterpret_cast<T*>(smem + SC::off_u);
+  T* E0 = reinterpret_cast<T*>(smem + SC::off_e);
+  T* E1 = reinterpret_cast<T*>(smem + SC::off_e + G::e_bytes);
+  T* E2 = reinterpret_cast<T*>(smem + SC::off_e + 2 * G::e_bytes);
+  unsigned char* gRing = smem + SC::off_g;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t barU = smem_u32(smem + SC::off_bar);
+  const uint32_t barG = barU + 8;            // `full` barriers of the ring slots
+  const uint32_t barE = barG + 8 * NG;       // `empty` barriers
+  auto block_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(SC::NT) : "memory"); };
+
+  const int te = min(tid, SC::ACTIVE - 1);
+  const int c = te / N2, p = te - c * N2;
+  const int hi = p / N1, lo = p - hi * N1;
+  const long long my_tiles = (long long)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const size_t g_stride = (size_t)gridDim.x * C * ND * RB;
+
+  if (tid == 0)
+  {
+    mbar_init(barU, 1);
+    for (int s = 0; s < NG; ++s)
+    {
+      mbar_init(barG + 8 * s, C);
+      mbar_init(barE + 8 * s, SC::NWARPS);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (warp == SC::NWARPS)
+  {
+    // ---- producer warp: lane k streams the planes of cell k of every tile of this block ----------------------
+    if (lane < C)
+    {
+      const unsigned char* src = reinterpret_cast<const unsigned char*>(Gm) + ((size_t)blockIdx.x * C + lane) * ND * RB;
+      const int par0 = SC::F32 ? ((lane * ND) & 1) : 0;
+      const uint32_t dst = smem_u32(gRing) + lane * SC::piece_stride;
+      constexpr uint32_t bytes0 = (uint32_t)up16(N2 * RB), bytes1 = (uint32_t)up16(N2 * RB + 8);
+      int slot = 0;
+      uint32_t epar = 1;
+      for (long long t = 0; t < my_tiles; ++t)
+      {
+#pragma unroll
+        for (int pl = 0; pl < N1; ++pl)
+        {
+          const int sh = SC::F32 ? ((par0 + pl * (N2 & 1)) & 1) : 0;
+          const uint32_t bytes = sh ? bytes1 : bytes0;
+          mbar_wait(barE + 8 * slot, epar);
+          mbar_expect_tx(barG + 8 * slot, bytes);
+          bulk_g2s(dst + slot * SC::slot_bytes, src + pl * (N2 * RB) - 8 * sh, bytes, barG + 8 * slot);
+          if (++slot == NG)
+          {
+            slot = 0;
+            epar ^= 1;
+          }
+        }
+        src += g_stride;
+      }
+    }
+    return;
+  }
+  long long tile = blockIdx.x;
+  if (tid == 0 && tile < ntiles)
+  {
+    mbar_expect_tx(barU, G::tile_bytes);
+    bulk_g2s(smem_u32(uS), U + (size_t)tile * C * ND, G::tile_bytes, barU);
+  }
+  // geometry reader offsets of my two cells (a piece = one cell's plane; fp32: 8-byte skew by record parity)
+  const int my_off0 = c * SC::piece_stride + RB * p;
+  const int my_off1 = my_off0 + CH * SC::piece_stride;
+  const int my_par0 = SC::F32 ? ((c * ND) & 1) : 0;
+  const int my_par1 = SC::F32 ? (((c + CH) * ND) & 1) : 0;
+  int c_slot = 0;
+  uint32_t c_par = 0;
+
+  uint32_t phase = 0;
+  for (; tile < ntiles; tile += gridDim.x, phase ^= 1)
+  {
+    const long long tn = tile + gridDim.x;
+    // ---- phase A: t = A2 u ------------------------------------------------------------------------------------
+    {
+      T y0[N1], y1[N1];
+      mbar_wait(barU, phase);
+      contract_in_x2(B.a, uS, col_base<Nat<N1>, PA>(c, hi, lo), CH * ND, 1, y0, y1);
+      col_store<XAB, PA>(E0, col_base<XAB, PA>(c, hi, lo), y0);
+      col_store<XAB, PA>(E0, col_base<XAB, PA>(c + CH, hi, lo), y1);
+    }
+    if (tid == 0)
+      bulk_wait_read0(); // the previous tile's W store has finished reading E2
+    block_sync(); // (1)
+    if (tid == 0 && tn < ntiles)
+    {
+      mbar_expect_tx(barU, G::tile_bytes);
+      bulk_g2s(smem_u32(uS), U + (size_t)tn * C * ND, G::tile_bytes, barU);
+    }
+    // ---- phase B: A1 A2 u and D1 A2 u ----------------------------------------------------------------------------
+    {
+      T ya0[N1], yd0[N1], ya1[N1], yd1[N1];
+      contract_in2_x2(B.a, B.d, E0, col_base<XAB, PB>(c, hi, lo), CH * XAB::Sc, xstride<XAB, 1>(), ya0, yd0, ya1, yd1);
+      col_store<XBC, PB>(E1, col_base<XBC, PB>(c, hi, lo), ya0);
+      col_store<XBC, PB>(E2, col_base<XBC, PB>(c, hi, lo), yd0);
+      col_store<XBC, PB>(E1, col_base<XBC, PB>(c + CH, hi, lo), ya1);
+      col_store<XBC, PB>(E2, col_base<XBC, PB>(c + CH, hi, lo), yd1);
+    }
+    block_sync(); // (2)
+    // ---- phase C: axis 0 forward, geometry, axis 0 backward, plane by plane (stiffness.hpp:68-77, :14-29, :95-97) --
+    {
+      T ta0[N1], td0[N1], ta1[N1], td1[N1], h0[N1], h1[N1];
+      col_load<XBC, PC>(E1, col_base<XBC, PC>(c, hi, lo), ta0);
+      col_load<XBC, PC>(E2, col_base<XBC, PC>(c, hi, lo), td0);
+      col_load<XBC, PC>(E1, col_base<XBC, PC>(c + CH, hi, lo), ta1);
+      col_load<XBC, PC>(E2, col_base<XBC, PC>(c + CH, hi, lo), td1);
+#pragma unroll
+      for (int i = 0; i < N1; ++i)
+        h0[i] = h1[i] = T(0);
+#pragma unroll(Roll<T, N1>::in)
+      for (int i0 = 0; i0 < N1; ++i0)
+      {
+        T w0a, w0b, w1a, w1b, w2a, w2b;
+        row_dot_x2<T, N1>(B.dt, i0 * LD, ta0, ta1, w0a, w0b);   // D(i0,:) ta
+        row_dot_x2<T, N1>(B.at, i0 * LD, td0, td1, w1a, w1b);   // A(i0,:) td
+        row_dot_x2<T, N1>(B.at, i0 * LD, ta0, ta1, w2a, w2b);   // A(i0,:) ta
+        mbar_wait(barG + 8 * c_slot, c_par);
+        const int sha = SC::F32 ? ((my_par0 + i0 * (N2 & 1)) & 1) : 0;
+        const int shb = SC::F32 ? ((my_par1 + i0 * (N2 & 1)) & 1) : 0;
+        const T* ga = reinterpret_cast<const T*>(gRing + c_slot * SC::slot_bytes + my_off0 + 8 * sha);
+        const T* gb = reinterpret_cast<const T*>(gRing + c_slot * SC::slot_bytes + my_off1 + 8 * shb);
+        T g0a, g1a, g2a, g0b, g1b, g2b;
+        if constexpr (sizeof(T) == 8)
+        {
+          const double2 a = *reinterpret_cast<const double2*>(ga);
+          const double2 b = *reinterpret_cast<const double2*>(gb);
+          g0a = a.x, g1a = a.y, g0b = b.x, g1b = b.y;
+        }
+        else
+        {
+          const float2 a = *reinterpret_cast<const float2*>(ga);
+          const float2 b = *reinterpret_cast<const float2*>(gb);
+          g0a = a.x, g1a = a.y, g0b = b.x, g1b = b.y;
+        }
+        g2a = ga[2], g2b = gb[2];
+        __syncwarp(); // every lane holds its records: hand the slot back to the producer
+        if (lane == 0)
+          mbar_arrive(barE + 8 * c_slot);
+        if (++c_slot == NG)
+        {
+          c_slot = 0;
+          c_par ^= 1;
+        }
+        const T fa = fma_t(g0a, w2a, fma_t(g1a, w1a, g2a * w0a));
+        const T fb = fma_t(g0b, w2b, fma_t(g1b, w1b, g2b * w0b));
+        T m[N1];
+        tab_run<T, N1>(B.a, i0 * LD, m);                        // A(:, i0)
+#pragma unroll
+        for (int i = 0; i < N1; ++i)
+        {
+          h0[i] = fma_t(m[i], fa, h0[i]);
+          h1[i] = fma_t(m[i], fb, h1[i]);
+        }
+      }
+      col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h0);
+      col_store<XBC, PC>(E0, col_base<XBC, PC>(c + CH, hi, lo), h1);
+    }
+    block_sync(); // (3)
+    // ---- phase B': back along axis 1 ------------------------------------------------------------------------------
+    {
+      T m0[N1], m1[N1];
+      contract_in_x2(B.a, E0, col_base<XBC, PB>(c, hi, lo), CH * XBC::Sc, xstride<XBC, 1>(), m0, m1);
+      col_store<XAB, PB>(E1, col_base<XAB, PB>(c, hi, lo), m0);
+      col_store<XAB, PB>(E1, col_base<XAB, PB>(c + CH, hi, lo), m1);
+    }
+    block_sync(); // (4)
+    // ---- phase A': back along axis 2 with the derivative matrix, W by bulk store -------------------------------------
+    {
+      T o0[N1], o1[N1];
+      contract_in_x2(B.d, E1, col_base<XAB, PA>(c, hi, lo), CH * XAB::Sc, xstride<XAB, 2>(), o0, o1);
+      col_store<Nat<N1>, PA>(E2, col_base<Nat<N1>, PA>(c, hi, lo), o0);
+      col_store<Nat<N1>, PA>(E2, col_base<Nat<N1>, PA>(c + CH, hi, lo), o1);
+      fence_proxy_async();
+      block_sync(); // (5)
+      if (tid == 0)
+      {
+        bulk_s2g(W + (size_t)tile * C * ND, smem_u32(E2), G::tile_bytes);
+        bulk_commit();
+      }
+    }
+  }
+  if (tid == 0)
+    bulk_wait_read0();
+}
+
 // ---- launch helpers --------------------------------------------------------------------------------------
 inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
@@ -1307,6 +1541,39 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
   return ntiles * C;
 }
 
+template <typename T, int N1, int C, int NG>
+long long run_stiff_col2(const StiffnessArgs<T>& a)
+{
+  using SC = StiffCol2<T, N1, C, NG>;
+  const long long ntiles = (long long)(a.num_cells / C);
+  if (ntiles == 0 || !al16(a.U) || !al16(a.W) || !al16(a.G))
+    return 0;
+  TabAD<T, N1> B;
+  fill_table<T, N1>(B.a, a.A_host, false);
+  fill_table<T, N1>(B.d, a.D_host, false);
+  fill_table<T, N1>(B.at, a.A_host, true);
+  fill_table<T, N1>(B.dt, a.D_host, true);
+  auto kernel = stiffness_column2_kernel<T, N1, C, NG>;
+  int bps = 0;
+  int rc = plan_blocks(kernel, SC::threads, SC::smem_bytes, bps);
+  if (rc)
+    return -rc;
+  const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
+  kernel<<<grid, SC::threads, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
+  count_launch();
+  if (cudaGetLastError() != cudaSuccess)
+    return -FEMTC_ERR_CUDA;
+  return ntiles * C;
+}
+// two cells per thread: tile sizes per shape (fp32 tiles must be whole 16-byte units)
+template <typename T, int N1>
+constexpr int cells2()
+{
+  if (N1 == 9) return sizeof(T) == 8 ? 2 : 4;
+  if (N1 == 7) return 4;
+  return 8; // n1 = 6
+}
+
 // Geometry transport per shape (REF_EXACT): depth of the block-wide producer-warp ring, 0 = warp-private rings.
 // Measured (profiles/r01_ab_producer_warp.txt, r01_ab_producer_warp_depth.txt; % of measured HBM, 1 M cells):
 //   fp32 n1=6  84 (private) -> 85 (3) -> 96 (5) -> 101 (8)      fp32 n1=7  69 -> 70 -> 78 -> 80
@@ -1337,6 +1604,18 @@ long long run_stiff_col_mode(const StiffnessArgs<T>& a)
       if (opt_variant() == 3)
         return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, 3, true>(a);
     return run_stiff_col<T, N1, C, FEMTC_STIFFNESS_FULL, NG, false>(a);
+  }
+  if constexpr (N1 == 6 || N1 == 7 || N1 == 9)
+  {
+    // Two cells per thread, n1 = 9 (profiles/r01_ab_stiffness_two_cells.txt; % of measured HBM, one -> two cells):
+    //   fp32 63 -> 66 (ring depth 3) -> 70 (5);  fp64 62 -> 68 (3) -> 64 (5).  n1 = 6, 7: within +-3 points, not used.
+    // variant 13 / 14 / 15 force it with ring depth 3 / 5 / 8; variant 4 forces the one-cell kernel.
+    const long long v = opt_variant();
+    if (v == 13) return run_stiff_col2<T, N1, cells2<T, N1>(), 3>(a);
+    if (v == 14) return run_stiff_col2<T, N1, cells2<T, N1>(), 5>(a);
+    if (v == 15) return run_stiff_col2<T, N1, cells2<T, N1>(), 8>(a);
+    if (N1 == 9 && (v == 0 || v == 1 || v == 2 || v == 9))
+      return sizeof(T) == 4 ? run_stiff_col2<T, N1, cells2<T, N1>(), 5>(a) : run_stiff_col2<T, N1, cells2<T, N1>(), 3>(a);
   }
   if constexpr (N1 >= 6)
   {

@@ -462,6 +462,29 @@ def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, vari
         femtc.set_option("variant", 0)
 
 
+@pytest.mark.parametrize("variant", (13, 14))   # two cells per thread, block-wide ring of depth 3 / 5
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", (5, 6, 8))
+def test_stiffness_two_cells_per_thread_parity(femtc, oracle, torch_cuda, P, dt, variant):
+    """REF_EXACT stiffness column kernel with two cells per thread: within tolerance of the oracle and
+    bit-identical to the one-cell kernel on the cells both serve from whole tiles."""
+    nc = {5: 148 * 8 * 7 + 9, 6: 148 * 4 * 9 + 3, 8: 148 * 4 * 7 + 1}[P]
+    femtc.set_option("tc", 0)
+    out = {}
+    try:
+        phi, U, geom = splitmix(oracle, "stiffness", P, nc, dt, seed=80 + P, centred=True)
+        ref = oracle_run(oracle, "stiffness", phi, U, geom, P, 0)
+        for v in (variant, 4):                               # 4: one cell per thread, warp-private rings
+            femtc.set_option("variant", v)
+            out[v] = run_device(femtc, torch_cuda, "stiffness", phi, U, geom, P, 0)
+            assert rel_err(out[v], ref) <= TOL[dt], (P, dt, v)
+        whole = (nc // 56) * 56 * (P + 1) ** 3
+        assert np.array_equal(out[variant][:whole], out[4][:whole])
+    finally:
+        femtc.set_option("variant", 0)
+        femtc.set_option("tc", -1)
+
+
 @pytest.mark.parametrize("variant", (10, 11))   # two cells per thread, tile = 1x / 2x the one-cell kernel's
 @pytest.mark.parametrize("P", (5, 6, 7, 8))
 def test_mass_two_cells_per_thread_parity(femtc, oracle, torch_cuda, P, variant):
