@@ -194,7 +194,9 @@ class ResidentOperator:
 
     def destroy(self) -> None:
         if getattr(self, "_h", None) is not None:
-            _lib.lib.femtc_operator_destroy(self._h)
+            lib = getattr(_lib, "lib", None) if _lib is not None else None  # module globals may be gone at exit
+            if lib is not None:
+                lib.femtc_operator_destroy(self._h)
             self._h = None
 
     __del__ = destroy
