@@ -462,6 +462,21 @@ def test_kernel_variants_parity(femtc, oracle, torch_cuda, op, mode, P, dt, vari
         femtc.set_option("variant", 0)
 
 
+@pytest.mark.parametrize("variant,P,dt", [(21, 5, "float32"), (20, 5, "float64"), (20, 6, "float32"), (20, 7, "float32")])
+def test_slab_and_column_mass_kernels_at_high_degree(femtc, oracle, torch_cuda, variant, P, dt):
+    """n1 = 6..8: the slab kernel (default for fp32 n1 = 6, variant 20 elsewhere) and the column kernel
+    (variant 21 at fp32 n1 = 6) both stay within tolerance of the oracle."""
+    nc = 148 * 4 * 5 * 3 + 7
+    phi, U, geom = splitmix(oracle, "mass", P, nc, dt, seed=90 + P, centred=True)
+    ref = oracle_run(oracle, "mass", phi, U, geom, P)
+    try:
+        for v in (0, variant):
+            femtc.set_option("variant", v)
+            assert rel_err(run_device(femtc, torch_cuda, "mass", phi, U, geom, P), ref) <= TOL[dt], (P, dt, v)
+    finally:
+        femtc.set_option("variant", 0)
+
+
 @pytest.mark.parametrize("variant", (13, 14))   # two cells per thread, block-wide ring of depth 3 / 5
 @pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("P", (5, 6, 8))
