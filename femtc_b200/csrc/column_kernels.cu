@@ -1661,6 +1661,8 @@ long long launch_mass_column(const MassArgs<T>& a)
     if (v == 10) two = 1;
     if (v == 11) two = 2;
     if (v == 12) two = 0;
+    if (v == 22 && n1 == 7) // development: one cell per thread, tile of 8 cells (392 of 416 lanes busy)
+      return run_mass_col<T, 7, 8>(a);
     if (two == 1)
       switch (n1)
       {
