@@ -38,6 +38,7 @@ def _load() -> C.CDLL:
         getattr(lib, f"femtc_gemm_micro_{s}").argtypes = [i] * 7 + [vp] * 3
         getattr(lib, f"femtc_gemm_strided_acc_{s}").argtypes = [i] * 8 + [vp] * 3
         getattr(lib, f"femtc_apply_contractions_{s}").argtypes = [i] * 3 + [vp] * 5 + [sz]
+        getattr(lib, f"femtc_apply_contractions_device_{s}").argtypes = [i] * 3 + [vp] * 5 + [sz, vp]
         getattr(lib, f"femtc_checksum_device_{s}").argtypes = [vp, sz, vp, vp]
         getattr(lib, f"femtc_fill_uniform_device_{s}").argtypes = [vp, sz, u64, u64, u64, i, vp]
         getattr(lib, f"femtc_operator_create_{s}").argtypes = [C.POINTER(vp), i, vp, sz, vp, sz, i, i]

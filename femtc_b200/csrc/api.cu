@@ -531,6 +531,47 @@ static int gemm_micro_host(int k, int m, int nc, int lda, int ldb, int ldc, int 
   return gemm_strided_host<T>(k, m, nc, 1, lda, ldb, 1, ldc, a, b, c);
 }
 
+// tmm_kernels.cu
+template <typename T>
+long long launch_tmm_tiled(int Na, int Nb, int Tr, const T* I0, const T* I1, const T* I2, const T* dB, T* dA,
+                           size_t batch, cudaStream_t s);
+
+// B, A device pointers; I0..I2 host pointers.  The tiled kernel serves whole tiles of the covered shapes, the
+// generic kernel everything else (ragged tail, other shapes, unaligned pointers) on the same stream.
+template <typename T>
+static int apply_contractions_device(int Na, int Nb, int Tr, const T* I0, const T* I1, const T* I2, const T* dB,
+                                     T* dA, size_t batch, cudaStream_t stream)
+{
+  if (Na < 1 || Nb < 1 || Na > 64 || Nb > 64 || !I0 || !I1 || !I2 || (batch && (!dA || !dB)))
+  {
+    set_error("bad apply_contractions shape or null pointer");
+    return FEMTC_ERR_ARG;
+  }
+  int rc = require_device();
+  if (rc || batch == 0)
+    return rc;
+  size_t done = 0;
+  if (g_opt_kernel.load() != 1)
+  {
+    const long long n = launch_tmm_tiled<T>(Na, Nb, Tr, I0, I1, I2, dB, dA, batch, stream);
+    if (n < 0)
+      return (int)-n;
+    done = (size_t)n;
+  }
+  if (done == batch)
+    return FEMTC_OK;
+  const size_t nm = (size_t)Na * Nb, nb3 = (size_t)Nb * Nb * Nb, na3 = (size_t)Na * Na * Na;
+  T* dI = nullptr;
+  FEMTC_CUDA(cudaMallocAsync(&dI, 3 * nm * sizeof(T), stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dI, I0, nm * sizeof(T), cudaMemcpyHostToDevice, stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dI + nm, I1, nm * sizeof(T), cudaMemcpyHostToDevice, stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dI + 2 * nm, I2, nm * sizeof(T), cudaMemcpyHostToDevice, stream));
+  rc = launch_apply_contractions<T>(Na, Nb, Tr, dI, dI + nm, dI + 2 * nm, dB + done * nb3, dA + done * na3,
+                                    batch - done, stream);
+  FEMTC_CUDA(cudaFreeAsync(dI, stream));
+  return rc;
+}
+
 template <typename T>
 static int apply_contractions_host(int Na, int Nb, int Tr, const T* I0, const T* I1, const T* I2,
                                    const T* B, T* A, size_t batch)
@@ -545,14 +586,11 @@ static int apply_contractions_host(int Na, int Nb, int Tr, const T* I0, const T*
     return rc;
   if (batch == 0)
     return FEMTC_OK;
-  const size_t nm = (size_t)Na * Nb, nb3 = (size_t)Nb * Nb * Nb, na3 = (size_t)Na * Na * Na;
-  DevBuf d0, d1, d2, dB, dA;
-  if ((rc = d0.upload(I0, sizeof(T) * nm)) || (rc = d1.upload(I1, sizeof(T) * nm)) ||
-      (rc = d2.upload(I2, sizeof(T) * nm)) || (rc = dB.upload(B, sizeof(T) * nb3 * batch)) ||
-      (rc = dA.alloc(sizeof(T) * na3 * batch)))
+  const size_t nb3 = (size_t)Nb * Nb * Nb, na3 = (size_t)Na * Na * Na;
+  DevBuf dB, dA;
+  if ((rc = dB.upload(B, sizeof(T) * nb3 * batch)) || (rc = dA.alloc(sizeof(T) * na3 * batch)))
     return rc;
-  if ((rc = launch_apply_contractions<T>(Na, Nb, Tr, (const T*)d0.p, (const T*)d1.p, (const T*)d2.p,
-                                         (const T*)dB.p, (T*)dA.p, batch, nullptr)))
+  if ((rc = apply_contractions_device<T>(Na, Nb, Tr, I0, I1, I2, (const T*)dB.p, (T*)dA.p, batch, nullptr)))
     return rc;
   FEMTC_CUDA(cudaMemcpy(A, dA.p, sizeof(T) * na3 * batch, cudaMemcpyDeviceToHost));
   return FEMTC_OK;
@@ -802,6 +840,17 @@ void femtc_operator_destroy(femtc_operator* h)
   if (op->dGeom)
     cudaFree(op->dGeom);
   delete op;
+}
+
+int femtc_apply_contractions_device_f64(int Na, int Nb, int Tr, const double* I0, const double* I1, const double* I2,
+                                        const double* dB, double* dA, size_t batch, void* stream)
+{
+  return apply_contractions_device<double>(Na, Nb, Tr, I0, I1, I2, dB, dA, batch, (cudaStream_t)stream);
+}
+int femtc_apply_contractions_device_f32(int Na, int Nb, int Tr, const float* I0, const float* I1, const float* I2,
+                                        const float* dB, float* dA, size_t batch, void* stream)
+{
+  return apply_contractions_device<float>(Na, Nb, Tr, I0, I1, I2, dB, dA, batch, (cudaStream_t)stream);
 }
 
 int femtc_string2order(const char* name)

@@ -159,6 +159,19 @@ int femtc_apply_contractions_f64(int Na, int Nb, int Tr, const double* I0, const
 int femtc_apply_contractions_f32(int Na, int Nb, int Tr, const float* I0, const float* I1,
                                  const float* I2, const float* B, float* A, size_t batch);
 
+/* The same contraction for tensors already in HBM: dB (batch*Nb^3) and dA (batch*Na^3) are DEVICE pointers,
+ * I0, I1, I2 stay HOST pointers (they travel as kernel parameters); asynchronous on `stream`.  Shapes
+ * Nb = 2..8 with Na = Nb-1 .. Nb+2 (restriction, collocation, over-integration by one or two points per
+ * direction -- quadrature points != DoFs) and 16-byte aligned pointers run on a tiled TMA kernel in which every
+ * tensor crosses HBM once in and once out ((Nb^3 + Na^3)*sizeof(T) bytes per tensor); every other shape is
+ * served by a slower general kernel.  The host-pointer entry points above use the same kernels. */
+int femtc_apply_contractions_device_f64(int Na, int Nb, int Tr, const double* I0, const double* I1,
+                                        const double* I2, const double* dB, double* dA, size_t batch,
+                                        void* stream);
+int femtc_apply_contractions_device_f32(int Na, int Nb, int Tr, const float* I0, const float* I1,
+                                        const float* I2, const float* dB, float* dA, size_t batch,
+                                        void* stream);
+
 /* linalg::string2order (reference src/linalg.hpp:21-37): returns 0..5, or -1 where the
  * reference throws std::runtime_error("Invalid loop order"). */
 int femtc_string2order(const char* name);

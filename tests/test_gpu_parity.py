@@ -321,6 +321,45 @@ def test_gemm_micro_strides_and_batched_tmm(femtc, oracle):
         assert rel_err(A[e * Na ** 3:(e + 1) * Na ** 3], ref) <= 1e-12
 
 
+TMM_SHAPES = [(Na, Nb) for Nb in range(2, 9) for Na in range(max(2, Nb - 1), Nb + 3)]
+
+
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("Tr", (0, 1))
+def test_batched_rectangular_contraction_kernel(femtc, oracle, torch_cuda, Tr, dt):
+    """apply_contractions on device tensors (femtc_apply_contractions_device_*): every shape of the tiled TMA
+    kernel (Nb = 2..8, Na = Nb-1..Nb+2), a batch of many tiles plus a ragged tail (generic kernel), against the
+    oracle tensor by tensor; the generic kernel forced on the same inputs must agree to rounding."""
+    torch = torch_cuda
+    rng = np.random.default_rng(11)
+    launches0 = femtc.get_option("launches")
+    for Na, Nb in TMM_SHAPES + [(9, 9), (3, 6)]:               # the last two: shapes only the generic kernel serves
+        batch = 148 * 4 * 3 + 5
+        I = [(rng.random(Na * Nb) - 0.5).astype(dt) for _ in range(3)]
+        B = (rng.random(batch * Nb ** 3) - 0.5).astype(dt)
+        dB = torch.from_numpy(B).cuda()
+        dA = torch.full((batch * Na ** 3,), float("nan"), dtype=dB.dtype, device="cuda")
+        femtc.apply_contractions(*I, dB, dA, Na, Nb, bool(Tr), batch=batch)
+        torch.cuda.synchronize()
+        A = dA.cpu().numpy()
+        assert np.isfinite(A).all()
+        for e in (0, 1, 7, batch // 2, batch - 6, batch - 1):   # first / interior tiles and the tail
+            _, ref = oracle.apply_contractions(Na, Nb, Tr, *I, B[e * Nb ** 3:(e + 1) * Nb ** 3])
+            assert rel_err(A[e * Na ** 3:(e + 1) * Na ** 3], ref) <= TOL[dt], (Na, Nb, Tr, dt, e)
+        femtc.set_option("kernel", 1)
+        try:
+            dA2 = torch.empty_like(dA)
+            femtc.apply_contractions(*I, dB, dA2, Na, Nb, bool(Tr), batch=batch)
+            torch.cuda.synchronize()
+        finally:
+            femtc.set_option("kernel", 0)
+        assert rel_err(dA2.cpu().numpy(), A) <= TOL[dt]
+        Ah = np.zeros(batch * Na ** 3, dtype=dt)               # host-pointer entry: same kernels
+        femtc.apply_contractions(*I, B, Ah, Na, Nb, bool(Tr), batch=batch)
+        assert np.array_equal(Ah, A)
+    assert femtc.get_option("launches") > launches0
+
+
 # ---- helpers of the measurement harness ----------------------------------------------------------------------
 @pytest.mark.parametrize("dt", DTYPES)
 def test_device_generator_and_checksum_match_host(femtc, oracle, torch_cuda, dt):
