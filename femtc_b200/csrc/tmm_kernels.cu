@@ -41,16 +41,27 @@ struct TmmPlan
 {
   static constexpr int NB2 = NB * NB, NB3 = NB2 * NB, NA2 = NA * NA, NA3 = NA2 * NA;
   static constexpr int widest = tmax(tmax(NB2, NA * NB), NA2);   // threads per tensor in the widest phase
-  // tensors per tile: about 256 threads, and whole 16-byte units for both bulk copies
-  static constexpr int C = tmax(4, (256 / widest) & ~3);
+  // tensors per tile: about TARGET threads (more for the small shapes, whose tiles would otherwise be a
+  // kilobyte or two and all barrier), and whole 16-byte units for both bulk copies
+#ifndef FEMTC_TMM_TARGET_SMALL
+#define FEMTC_TMM_TARGET_SMALL 512
+#endif
+#ifndef FEMTC_TMM_TARGET
+#define FEMTC_TMM_TARGET 256
+#endif
+  static constexpr int TARGET = widest <= 25 ? FEMTC_TMM_TARGET_SMALL : FEMTC_TMM_TARGET;
+  static constexpr int C = tmax(4, (TARGET / widest) & ~3);
   static constexpr int NT = (C * widest + 31) & ~31;
   static constexpr int LD1 = NB | 1;                              // padded row of S1: odd stride for phase 2
+  // S0 plane stride: phase 1 reads, for fixed b1, runs of NB values from consecutive (e, a0) planes; with the
+  // stride = NB (mod 32) those runs tile the banks instead of piling up (NB = 8: 64 -> 72)
+  static constexpr int LD0 = NB < 4 ? NB2 : NB2 + ((NB - NB2) % 32 + 32) % 32;
   static constexpr uint32_t in_bytes = C * NB3 * sizeof(T);
   static constexpr uint32_t out_bytes = C * NA3 * sizeof(T);
   static_assert(in_bytes % 16 == 0 && out_bytes % 16 == 0, "tiles must be whole 16-byte units");
   static constexpr int off_in = 0;
   static constexpr int off_s0 = off_in + tup128(in_bytes);
-  static constexpr int off_s1 = off_s0 + tup128(C * NA * NB2 * (int)sizeof(T));
+  static constexpr int off_s1 = off_s0 + tup128(C * NA * LD0 * (int)sizeof(T));
   static constexpr int off_out = off_s1 + tup128(C * NA2 * LD1 * (int)sizeof(T));
   static constexpr int off_bar = off_out + tup128(out_bytes);
   static constexpr int smem_bytes = off_bar + 16;
@@ -61,7 +72,7 @@ __global__ void __launch_bounds__(TmmPlan<T, NA, NB>::NT)
 tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B, T* __restrict__ A, long long ntiles)
 {
   using PL = TmmPlan<T, NA, NB>;
-  constexpr int C = PL::C, NB2 = PL::NB2, NB3 = PL::NB3, NA2 = PL::NA2, NA3 = PL::NA3, LD1 = PL::LD1;
+  constexpr int C = PL::C, NB2 = PL::NB2, NB3 = PL::NB3, NA2 = PL::NA2, NA3 = PL::NA3, LD1 = PL::LD1, LD0 = PL::LD0;
   extern __shared__ __align__(128) unsigned char smem[];
   T* inS = reinterpret_cast<T*>(smem + PL::off_in);
   T* s0 = reinterpret_cast<T*>(smem + PL::off_s0);
@@ -103,7 +114,7 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 #pragma unroll
         for (int b = 0; b < NB; ++b)
           acc = fma_t(M.i0[a * NB + b], x[b], acc);
-        s0[(e * NA + a) * NB2 + d] = acc;
+        s0[(e * NA + a) * LD0 + d] = acc;
       }
     }
     __syncthreads(); // (1) input staging consumed, S0 complete
@@ -119,7 +130,7 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
       T x[NB];
 #pragma unroll
       for (int b = 0; b < NB; ++b)
-        x[b] = s0[(e * NA + a0) * NB2 + b * NB + b2];
+        x[b] = s0[(e * NA + a0) * LD0 + b * NB + b2];
 #pragma unroll
       for (int a = 0; a < NA; ++a)
       {
@@ -141,6 +152,7 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 #pragma unroll
       for (int b = 0; b < NB; ++b)
         x[b] = s1[tid * LD1 + b];
+      T y[NA];
 #pragma unroll
       for (int a = 0; a < NA; ++a)
       {
@@ -148,7 +160,33 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 #pragma unroll
         for (int b = 0; b < NB; ++b)
           acc = fma_t(M.i2[a * NB + b], x[b], acc);
-        outS[tid * NA + a] = acc;
+        y[a] = acc;
+      }
+      // a thread's NA outputs are contiguous: 16-byte stores where the row allows it cut the bank conflicts of
+      // the even row strides (NA = 8 fp32: 8-way on scalar stores, 2-way on 128-bit stores)
+      constexpr int V = 16 / (int)sizeof(T);
+      if constexpr ((NA * sizeof(T)) % 16 == 0)
+      {
+#pragma unroll
+        for (int a = 0; a < NA; a += V)
+        {
+          if constexpr (sizeof(T) == 4)
+            *reinterpret_cast<float4*>(outS + tid * NA + a) = make_float4(y[a], y[a + 1], y[a + 2], y[a + 3]);
+          else
+            *reinterpret_cast<double2*>(outS + tid * NA + a) = make_double2(y[a], y[a + 1]);
+        }
+      }
+      else if constexpr ((NA * sizeof(T)) % 8 == 0 && sizeof(T) == 4)
+      {
+#pragma unroll
+        for (int a = 0; a < NA; a += 2)
+          *reinterpret_cast<float2*>(outS + tid * NA + a) = make_float2(y[a], y[a + 1]);
+      }
+      else
+      {
+#pragma unroll
+        for (int a = 0; a < NA; ++a)
+          outS[tid * NA + a] = y[a];
       }
     }
     fence_proxy_async();
