@@ -77,3 +77,14 @@ void apply_contractions(const T* I0, const T* I1, const T* I2, T* __restrict__ B
   if (rc != FEMTC_OK)
     linalg::detail::fail(rc);
 }
+
+/// Extension (no counterpart in the reference): the same contraction applied to `batch` tensors stored back to
+/// back -- B holds batch*Nb^3 values, A receives batch*Na^3 -- in one call, i.e. one pipelined pass of the tiled
+/// device kernel (femtc_b200/csrc/tmm_kernels.cu) instead of `batch` single-tensor round trips.  Host pointers.
+template <typename T, int Na, int Nb, bool Tr>
+void apply_contractions_batched(const T* I0, const T* I1, const T* I2, const T* B, T* A, std::size_t batch)
+{
+  const int rc = linalg::detail::abi<T>::contractions(Na, Nb, Tr ? 1 : 0, I0, I1, I2, B, A, batch);
+  if (rc != FEMTC_OK)
+    linalg::detail::fail(rc);
+}

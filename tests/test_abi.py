@@ -148,6 +148,7 @@ template <typename T> int use()
   linalg::gemm_micro<T, 4, 4, 16, 4, 16, 16>(phi.data(), U.data(), W.data());
   Buffer<T, 4, 4> buf;
   apply_contractions<T, 4, 4, true>(phi.data(), phi.data(), phi.data(), U.data(), W.data(), buf);
+  apply_contractions_batched<T, 4, 4, false>(phi.data(), phi.data(), phi.data(), U.data(), W.data(), 1);
   contract<T, 4, 4, 4, 4, false>(phi.data(), U.data(), W.data());
   contract<T, 4, 4, 4>(phi.data(), U.data(), W.data());
   transpose<T, 4, 4, 4, 16, 4, 1>(U.data(), W.data());
