@@ -214,8 +214,12 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
  *                     or 1 when FEMTC_HOST_REGISTER=1 is in the environment at load time.
  *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
  *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
- *   "variant"         development knob: alternative pipeline depths of a kernel family (0 = tuned default;
- *                     9 = one-thread-per-cell family off).  Results never depend on it.
+ *   "variant"         development knob for A/B measurements (0 = tuned defaults).  1, 2: alternative pipeline
+ *                     depths; 9: one-thread-per-cell family off; 3..8: geometry transport of the column
+ *                     stiffness kernels (producer warp / warp-private rings, ring depths); 10..12: mass column
+ *                     kernels with two cells / one cell per thread; 13..15: two-cell stiffness kernel;
+ *                     20, 21: slab kernel on / off at n1 = 6..8.  Results never depend on it beyond rounding
+ *                     (kernels of one family are bit-identical; tests/test_gpu_parity.py).
  *   "launches"        (read-only) kernels launched by this library so far in this process */
 int femtc_set_option(const char* name, long long value);
 long long femtc_get_option(const char* name);
