@@ -825,7 +825,8 @@ struct StiffCol
   static constexpr int off_g = off_e + NE * G::e_bytes;
   static constexpr int off_bar = off_g + ring_bytes;
   static constexpr int smem_bytes = off_bar + 8 * n_bars + 8;
-  static constexpr int min_blocks = min_blocks_for(threads, smem_bytes, sizeof(T) == 8 ? (FULL ? 128 : 104) : (FULL ? ((N1 == 7 || N1 == 8) ? 88 : 104) : 72))  // FULL fp32 n1 = 7, 8: a third / second resident block is worth 28 bytes of spills (42 -> 45 %, 56 -> 60 %);
+  static constexpr int min_blocks = min_blocks_for(threads, smem_bytes, sizeof(T) == 8 ? (FULL ? 128 : 104) : (FULL ? ((N1 == 7 || N1 == 8) ? 88 : 104) : 72));
+  // (FULL fp32 n1 = 7, 8: one more resident block is worth 28 bytes of spills: 42 -> 45 %, 56 -> 60 % of measured HBM)
 };
 
 template <typename T, int N1, int C, int MODE, int NG, bool PW>
