@@ -41,17 +41,16 @@ struct TmmPlan
 {
   static constexpr int NB2 = NB * NB, NB3 = NB2 * NB, NA2 = NA * NA, NA3 = NA2 * NA;
   static constexpr int widest = tmax(tmax(NB2, NA * NB), NA2);   // threads per tensor in the widest phase
-  // tensors per tile: about TARGET threads (more for the small shapes, whose tiles would otherwise be a
-  // kilobyte or two and all barrier), and whole 16-byte units for both bulk copies
-#ifndef FEMTC_TMM_TARGET_SMALL
-#define FEMTC_TMM_TARGET_SMALL 512
+  // tensors per tile: enough for about 256 threads in the widest phase, and at least ~16 KB of output so that
+  // the four block barriers and the two bulk copies of a tile are amortised for the small shapes too (threads
+  // then loop over the tile); always whole 16-byte units for both bulk copies
+#ifndef FEMTC_TMM_MIN_OUT_BYTES
+#define FEMTC_TMM_MIN_OUT_BYTES 16384
 #endif
-#ifndef FEMTC_TMM_TARGET
-#define FEMTC_TMM_TARGET 256
-#endif
-  static constexpr int TARGET = widest <= 25 ? FEMTC_TMM_TARGET_SMALL : FEMTC_TMM_TARGET;
-  static constexpr int C = tmax(4, (TARGET / widest) & ~3);
-  static constexpr int NT = (C * widest + 31) & ~31;
+  static constexpr int c_threads = (256 / widest) & ~3;
+  static constexpr int c_bytes = (FEMTC_TMM_MIN_OUT_BYTES / (NA3 * (int)sizeof(T))) & ~3;
+  static constexpr int C = tmax(4, tmax(c_threads, c_bytes));
+  static constexpr int NT = C * widest >= 512 ? 512 : ((C * widest + 31) & ~31);
   static constexpr int LD1 = NB | 1;                              // padded row of S1: odd stride for phase 2
   // S0 plane stride: phase 1 reads, for fixed b1, runs of NB values from consecutive (e, a0) planes; with the
   // stride = NB (mod 32) those runs tile the banks instead of piling up (NB = 8: 64 -> 72)
@@ -100,9 +99,9 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
     const long long tn = tile + gridDim.x;
     // ---- phase 0: axis 0 (tmm.hpp:100-104) -----------------------------------------------------------
     mbar_wait(bar, phase);
-    if (tid < C * NB2)
+    for (int idx = tid; idx < C * NB2; idx += PL::NT)
     {
-      const int e = tid / NB2, d = tid - e * NB2;
+      const int e = idx / NB2, d = idx - e * NB2;
       T x[NB];
 #pragma unroll
       for (int b = 0; b < NB; ++b)
@@ -124,9 +123,9 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
       bulk_g2s(smem_u32(inS), B + (size_t)tn * C * NB3, PL::in_bytes, bar);
     }
     // ---- phase 1: axis 1 (tmm.hpp:108-112) -----------------------------------------------------------
-    if (tid < C * NA * NB)
+    for (int idx = tid; idx < C * NA * NB; idx += PL::NT)
     {
-      const int e = tid / (NA * NB), r = tid - e * (NA * NB), a0 = r / NB, b2 = r - a0 * NB;
+      const int e = idx / (NA * NB), r = idx - e * (NA * NB), a0 = r / NB, b2 = r - a0 * NB;
       T x[NB];
 #pragma unroll
       for (int b = 0; b < NB; ++b)
@@ -146,12 +145,12 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
     if (tid == 0)
       bulk_wait_read0(); // the previous tile's store has finished reading outS
     __syncthreads();     // (3)
-    if (tid < C * NA2)
+    for (int row = tid; row < C * NA2; row += PL::NT)
     {
       T x[NB];
 #pragma unroll
       for (int b = 0; b < NB; ++b)
-        x[b] = s1[tid * LD1 + b];
+        x[b] = s1[row * LD1 + b];
       T y[NA];
 #pragma unroll
       for (int a = 0; a < NA; ++a)
@@ -171,22 +170,22 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
         for (int a = 0; a < NA; a += V)
         {
           if constexpr (sizeof(T) == 4)
-            *reinterpret_cast<float4*>(outS + tid * NA + a) = make_float4(y[a], y[a + 1], y[a + 2], y[a + 3]);
+            *reinterpret_cast<float4*>(outS + row * NA + a) = make_float4(y[a], y[a + 1], y[a + 2], y[a + 3]);
           else
-            *reinterpret_cast<double2*>(outS + tid * NA + a) = make_double2(y[a], y[a + 1]);
+            *reinterpret_cast<double2*>(outS + row * NA + a) = make_double2(y[a], y[a + 1]);
         }
       }
       else if constexpr ((NA * sizeof(T)) % 8 == 0 && sizeof(T) == 4)
       {
 #pragma unroll
         for (int a = 0; a < NA; a += 2)
-          *reinterpret_cast<float2*>(outS + tid * NA + a) = make_float2(y[a], y[a + 1]);
+          *reinterpret_cast<float2*>(outS + row * NA + a) = make_float2(y[a], y[a + 1]);
       }
       else
       {
 #pragma unroll
         for (int a = 0; a < NA; ++a)
-          outS[tid * NA + a] = y[a];
+          outS[row * NA + a] = y[a];
       }
     }
     fence_proxy_async();
