@@ -321,6 +321,37 @@ def test_gemm_micro_strides_and_batched_tmm(femtc, oracle):
         assert rel_err(A[e * Na ** 3:(e + 1) * Na ** 3], ref) <= 1e-12
 
 
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", range(1, 9))
+def test_no_write_outside_the_output_field(femtc, oracle, torch_cuda, P, dt):
+    """Guard bands: W sits inside a larger allocation whose margins hold a sentinel; no kernel family (default
+    dispatch and every development variant that changes tiling) may touch a byte outside [W, W + n)."""
+    torch = torch_cuda
+    nd = (P + 1) ** 3
+    nc = {1: 4099, 2: 2053, 3: 1031, 4: 523, 5: 263, 6: 131, 7: 67, 8: 37}[P] * 3
+    tdt = {"float64": torch.float64, "float32": torch.float32}[dt]
+    guard = 4096                                              # elements, keeps W 16-byte aligned
+    for op, gw in (("mass", 1), ("stiffness", 6)):
+        phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=70 + P, centred=True)
+        dU, dG = torch.from_numpy(U).cuda(), torch.from_numpy(geom).cuda()
+        for variant in (0, 3, 5, 6, 7, 10, 11, 13, 14, 20):
+            for mode in ((0,) if op == "mass" else (0, 1)):
+                buf = torch.full((nc * nd + 2 * guard,), -777.0, dtype=tdt, device="cuda")
+                W = buf[guard:guard + nc * nd]
+                femtc.set_option("variant", variant)
+                try:
+                    if op == "mass":
+                        femtc.mass_operator(phi, dU, W, dG, nc, P)
+                    else:
+                        femtc.stiffness_operator(phi, dU, W, dG, nc, P, mode=mode)
+                    torch.cuda.synchronize()
+                finally:
+                    femtc.set_option("variant", 0)
+                assert bool((buf[:guard] == -777.0).all()) and bool((buf[guard + nc * nd:] == -777.0).all()), \
+                    (op, P, dt, variant, mode)
+                assert bool(torch.isfinite(W).all())
+
+
 TMM_SHAPES = [(Na, Nb) for Nb in range(2, 9) for Na in range(max(2, Nb - 1), Nb + 3)]
 
 
