@@ -120,6 +120,60 @@ __device__ __forceinline__ void tab_run(const T* M, int off, T (&m)[N1])
   }
 }
 
+// y[i] += m[i] * x for a whole column.  fp32: two outputs per instruction (FFMA2, fma.rn.f32x2 -- the table pair
+// {m[i], m[i+1]} is a 64-bit uniform-register operand, x is broadcast); each lane result is the same IEEE fma as
+// the scalar form, so nothing changes bitwise, but the FMA instruction count of the issue-bound fp32 kernels halves
+// (probe: tools/probe/ffma2_probe.cu, same 74 TFLOP/s from half the issue slots).
+#ifndef FEMTC_FFMA2
+#define FEMTC_FFMA2 1
+#endif
+template <typename T, int N1>
+__device__ __forceinline__ void axpy_n(const T (&m)[N1], T x, T (&y)[N1])
+{
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  {
+    const float2 xx = make_float2(x, x);
+#pragma unroll
+    for (int i = 0; i + 1 < N1; i += 2)
+    {
+      const float2 r = __ffma2_rn(make_float2(m[i], m[i + 1]), xx, make_float2(y[i], y[i + 1]));
+      y[i] = r.x, y[i + 1] = r.y;
+    }
+    if constexpr (N1 & 1)
+      y[N1 - 1] = fma_t(m[N1 - 1], x, y[N1 - 1]);
+  }
+  else
+  {
+#pragma unroll
+    for (int i = 0; i < N1; ++i)
+      y[i] = fma_t(m[i], x, y[i]);
+  }
+}
+// {r0, r1} = sum_p m[p] * {z0[p], z1[p]}: one table row against the same column of two cells
+template <typename T, int N1>
+__device__ __forceinline__ void dot2_n(const T (&m)[N1], const T (&z0)[N1], const T (&z1)[N1], T& r0, T& r1)
+{
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  {
+    float2 acc = __fmul2_rn(make_float2(m[0], m[0]), make_float2(z0[0], z1[0]));
+#pragma unroll
+    for (int p = 1; p < N1; ++p)
+      acc = __ffma2_rn(make_float2(m[p], m[p]), make_float2(z0[p], z1[p]), acc);
+    r0 = acc.x, r1 = acc.y;
+  }
+  else
+  {
+    T a0 = m[0] * z0[0], a1 = m[0] * z1[0];
+#pragma unroll
+    for (int p = 1; p < N1; ++p)
+    {
+      a0 = fma_t(m[p], z0[p], a0);
+      a1 = fma_t(m[p], z1[p], a1);
+    }
+    r0 = a0, r1 = a1;
+  }
+}
+
 // One trip: columns p0 .. p0+CNT-1 of the tables (table offset `off` = p0*LD) applied to the values
 // at ptr[0], ptr[stride], ...
 template <int CNT, bool DUAL, typename T, int N1>
@@ -136,15 +190,11 @@ __device__ __forceinline__ void contract_in_trip(const T* Ma, const T* Mb, int o
   {
     T m[N1];
     tab_run<T, N1>(Ma, off + u * LD, m);
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-      ya[i] = fma_t(m[i], xp[u], ya[i]);
+    axpy_n<T, N1>(m, xp[u], ya);
     if constexpr (DUAL)
     {
       tab_run<T, N1>(Mb, off + u * LD, m);
-#pragma unroll
-      for (int i = 0; i < N1; ++i)
-        yb[i] = fma_t(m[i], xp[u], yb[i]);
+      axpy_n<T, N1>(m, xp[u], yb);
     }
   }
 }
@@ -254,9 +304,7 @@ __device__ __forceinline__ void col_axpy(const T (&M)[N1 * tab_ld<N1>()], int p,
 {
   T m[N1];
   tab_run<T, N1>(M, p * tab_ld<N1>(), m);
-#pragma unroll
-  for (int i = 0; i < N1; ++i)
-    y[i] = fma_t(m[i], f, y[i]);
+  axpy_n<T, N1>(m, f, y);
 }
 
 // ---- two cells per thread -------------------------------------------------------------------------------
@@ -281,12 +329,8 @@ __device__ __forceinline__ void contract_in_trip_x2(const T* M, int off, const T
   {
     T m[N1];
     tab_run<T, N1>(M, off + u * LD, m);
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-    {
-      y0[i] = fma_t(m[i], xa[u], y0[i]);
-      y1[i] = fma_t(m[i], xb[u], y1[i]);
-    }
+    axpy_n<T, N1>(m, xa[u], y0);
+    axpy_n<T, N1>(m, xb[u], y1);
   }
 }
 // y0[i] = sum_p A(i,p) buf[base + p*stride],  y1[i] = sum_p A(i,p) buf[base + delta + p*stride]
@@ -335,19 +379,11 @@ __device__ __forceinline__ void contract_in2_trip_x2(const T* Ma, const T* Mb, i
   {
     T m[N1];
     tab_run<T, N1>(Ma, off + u * LD, m);
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-    {
-      ya0[i] = fma_t(m[i], xa[u], ya0[i]);
-      ya1[i] = fma_t(m[i], xb[u], ya1[i]);
-    }
+    axpy_n<T, N1>(m, xa[u], ya0);
+    axpy_n<T, N1>(m, xb[u], ya1);
     tab_run<T, N1>(Mb, off + u * LD, m);
-#pragma unroll
-    for (int i = 0; i < N1; ++i)
-    {
-      yb0[i] = fma_t(m[i], xa[u], yb0[i]);
-      yb1[i] = fma_t(m[i], xb[u], yb1[i]);
-    }
+    axpy_n<T, N1>(m, xa[u], yb0);
+    axpy_n<T, N1>(m, xb[u], yb1);
   }
 }
 template <typename T, int N1>
@@ -384,14 +420,7 @@ __device__ __forceinline__ void row_dot_x2(const T* MT, int off, const T (&z0)[N
 {
   T m[N1];
   tab_run<T, N1>(MT, off, m);
-  T a0 = m[0] * z0[0], a1 = m[0] * z1[0];
-#pragma unroll
-  for (int p = 1; p < N1; ++p)
-  {
-    a0 = fma_t(m[p], z0[p], a0);
-    a1 = fma_t(m[p], z1[p], a1);
-  }
-  r0 = a0, r1 = a1;
+  dot2_n<T, N1>(m, z0, z1, r0, r1);
 }
 template <typename T, int N1>
 __device__ __forceinline__ void contract_out_x2(const T (&MT)[N1 * tab_ld<N1>()], const T (&z0)[N1], const T (&z1)[N1], T* buf,
@@ -1405,12 +1434,8 @@ stiffness_column2_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __rest
         const T fb = fma_t(g0b, w2b, fma_t(g1b, w1b, g2b * w0b));
         T m[N1];
         tab_run<T, N1>(B.a, i0 * LD, m);                        // A(:, i0)
-#pragma unroll
-        for (int i = 0; i < N1; ++i)
-        {
-          h0[i] = fma_t(m[i], fa, h0[i]);
-          h1[i] = fma_t(m[i], fb, h1[i]);
-        }
+        axpy_n<T, N1>(m, fa, h0);
+        axpy_n<T, N1>(m, fb, h1);
       }
       col_store<XBC, PC>(E0, col_base<XBC, PC>(c, hi, lo), h0);
       col_store<XBC, PC>(E0, col_base<XBC, PC>(c + CH, hi, lo), h1);
