@@ -272,6 +272,25 @@ template <typename T, int N1>
 __device__ __forceinline__ void contract_out(const T (&MT)[N1 * tab_ld<N1>()], const T (&z)[N1], T* buf, int base, int stride)
 {
   constexpr int LD = tab_ld<N1>();
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  {
+    // fp32: rows i, i+1 together.  MT[p + i*LD] = A(i,p); the pair {A(i,p), A(i+1,p)} is gathered from two rows of
+    // the transposed table (constant-bank operands), z[p] is broadcast; lane results equal the scalar form's.
+    T* ptr = buf + base;
+#pragma unroll
+    for (int i = 0; i + 1 < N1; i += 2)
+    {
+      float2 acc = __fmul2_rn(make_float2(MT[i * LD], MT[(i + 1) * LD]), make_float2(z[0], z[0]));
+#pragma unroll
+      for (int p = 1; p < N1; ++p)
+        acc = __ffma2_rn(make_float2(MT[p + i * LD], MT[p + (i + 1) * LD]), make_float2(z[p], z[p]), acc);
+      ptr[i * stride] = acc.x;
+      ptr[(i + 1) * stride] = acc.y;
+    }
+    if constexpr (N1 & 1)
+      ptr[(N1 - 1) * stride] = row_dot_off<T, N1>(MT, (N1 - 1) * LD, z);
+    return;
+  }
   constexpr int U = Roll<T, N1>::in;
   constexpr int TRIPS = N1 / U, REM = N1 - TRIPS * U;
   T* ptr = buf + base;
@@ -1106,12 +1125,15 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
       for (int i0 = 0; i0 < N1; ++i0)
       {
         const T w0 = row_dot(B.dt, i0, ta);
-        const T w1 = row_dot(B.at, i0, td);
-        T w2;
-        if constexpr (FULL)
-          w2 = row_dot(B.at, i0, sa);
-        else
-          w2 = row_dot(B.at, i0, ta);
+        T w1, w2; // one table row against two columns (fp32: one FFMA2 per entry)
+        {
+          T mrow[N1];
+          tab_run<T, N1>(B.at, i0 * tab_ld<N1>(), mrow);
+          if constexpr (FULL)
+            dot2_n<T, N1>(mrow, td, sa, w1, w2);
+          else
+            dot2_n<T, N1>(mrow, td, ta, w1, w2);
+        }
         mbar_wait(barG + 8 * c_slot, c_par);
         const int sh = SC::F32 ? ((my_par + i0 * (N2 & 1)) & 1) : 0;
         const T* gp = reinterpret_cast<const T*>(gRing + c_slot * SC::slot_bytes + my_off + 8 * sh);

@@ -12,7 +12,7 @@
 //     phase 2   thread (e, a0, a1)   row    along b2 of S1                 ->  out[e][a0][a1][a2]   (natural order)
 // Input tiles arrive by one TMA bulk copy (requested for the block's next tile as soon as phase 0 has read the
 // current one), output tiles leave by one bulk store.  The three Na x Nb matrices are kernel parameters
-// (constant bank), already in I(a,b) = m[a*Nb + b] form whatever the caller's `Tr`.  Sums run over b ascending
+// (constant bank), already in I(a,b) = m[b*Na + a] form whatever the caller's `Tr`.  Sums run over b ascending
 // from zero, as the reference's accumulate-into-zeroed-buffer does (tmm.hpp:24-32, :65-85).
 //
 // Algorithmic HBM bytes per tensor: (Nb^3 + Na^3) * sizeof(T).
@@ -28,13 +28,56 @@ namespace
 constexpr int tmax(int a, int b) { return a > b ? a : b; }
 constexpr int tup128(int bytes) { return (bytes + 127) & ~127; }
 
+#ifndef FEMTC_FFMA2
+#define FEMTC_FFMA2 1
+#endif
+// Tables in [b][a] order, I(a,b) = m[b*NA + a]: the outputs a, a+1 of one input b are neighbours, which is what
+// the packed fp32 FMA (FFMA2) wants as its table operand.
 template <typename T, int NA, int NB>
-struct TmmTab
+struct alignas(16) TmmTab
 {
   T i0[NA * NB];
   T i1[NA * NB];
   T i2[NA * NB];
 };
+
+// y[a] = sum_b I(a,b) x[b], b ascending from zero (tmm.hpp:24-32); fp32 computes a, a+1 together
+template <typename T, int NA, int NB>
+__device__ __forceinline__ void tmm_column(const T (&m)[NA * NB], const T (&x)[NB], T (&y)[NA])
+{
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  {
+#pragma unroll
+    for (int a = 0; a + 1 < NA; a += 2)
+    {
+      float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        acc = __ffma2_rn(make_float2(m[b * NA + a], m[b * NA + a + 1]), make_float2(x[b], x[b]), acc);
+      y[a] = acc.x, y[a + 1] = acc.y;
+    }
+    if constexpr (NA & 1)
+    {
+      T acc = T(0);
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        acc = fma_t(m[b * NA + NA - 1], x[b], acc);
+      y[NA - 1] = acc;
+    }
+  }
+  else
+  {
+#pragma unroll
+    for (int a = 0; a < NA; ++a)
+    {
+      T acc = T(0);
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+        acc = fma_t(m[b * NA + a], x[b], acc);
+      y[a] = acc;
+    }
+  }
+}
 
 template <typename T, int NA, int NB>
 struct TmmPlan
@@ -106,15 +149,11 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 #pragma unroll
       for (int b = 0; b < NB; ++b)
         x[b] = inS[e * NB3 + b * NB2 + d];
+      T y[NA];
+      tmm_column<T, NA, NB>(M.i0, x, y);
 #pragma unroll
       for (int a = 0; a < NA; ++a)
-      {
-        T acc = T(0);
-#pragma unroll
-        for (int b = 0; b < NB; ++b)
-          acc = fma_t(M.i0[a * NB + b], x[b], acc);
-        s0[(e * NA + a) * LD0 + d] = acc;
-      }
+        s0[(e * NA + a) * LD0 + d] = y[a];
     }
     __syncthreads(); // (1) input staging consumed, S0 complete
     if (tid == 0 && tn < ntiles)
@@ -130,15 +169,11 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 #pragma unroll
       for (int b = 0; b < NB; ++b)
         x[b] = s0[(e * NA + a0) * LD0 + b * NB + b2];
+      T y[NA];
+      tmm_column<T, NA, NB>(M.i1, x, y);
 #pragma unroll
       for (int a = 0; a < NA; ++a)
-      {
-        T acc = T(0);
-#pragma unroll
-        for (int b = 0; b < NB; ++b)
-          acc = fma_t(M.i1[a * NB + b], x[b], acc);
-        s1[((e * NA + a0) * NA + a) * LD1 + b2] = acc;
-      }
+        s1[((e * NA + a0) * NA + a) * LD1 + b2] = y[a];
     }
     __syncthreads(); // (2)
     // ---- phase 2: axis 2 (tmm.hpp:116-120), natural-order output tile -------------------------------------
@@ -152,15 +187,7 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
       for (int b = 0; b < NB; ++b)
         x[b] = s1[row * LD1 + b];
       T y[NA];
-#pragma unroll
-      for (int a = 0; a < NA; ++a)
-      {
-        T acc = T(0);
-#pragma unroll
-        for (int b = 0; b < NB; ++b)
-          acc = fma_t(M.i2[a * NB + b], x[b], acc);
-        y[a] = acc;
-      }
+      tmm_column<T, NA, NB>(M.i2, x, y);
       // a thread's NA outputs are contiguous: 16-byte stores where the row allows it cut the bank conflicts of
       // the even row strides (NA = 8 fp32: 8-way on scalar stores, 2-way on 128-bit stores)
       constexpr int V = 16 / (int)sizeof(T);
@@ -202,13 +229,13 @@ tmm_kernel(const __grid_constant__ TmmTab<T, NA, NB> M, const T* __restrict__ B,
 
 inline bool tal16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-// I(a,b) in row-major [a][b] form from the caller's layout (tmm.hpp:65-85: Tr ? I[a*Nb+b] : I[b*Na+a])
+// I(a,b) in [b][a] form from the caller's layout (tmm.hpp:65-85: Tr ? I[a*Nb+b] : I[b*Na+a])
 template <typename T, int NA, int NB>
 void fill_tab(T* dst, const T* src, int Tr)
 {
   for (int a = 0; a < NA; ++a)
     for (int b = 0; b < NB; ++b)
-      dst[a * NB + b] = Tr ? src[a * NB + b] : src[b * NA + a];
+      dst[b * NA + a] = Tr ? src[a * NB + b] : src[b * NA + a];
 }
 
 template <typename T, int NA, int NB>
