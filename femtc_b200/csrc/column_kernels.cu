@@ -127,10 +127,12 @@ __device__ __forceinline__ void tab_run(const T* M, int off, T (&m)[N1])
 #ifndef FEMTC_FFMA2
 #define FEMTC_FFMA2 1
 #endif
-template <typename T, int N1>
+// PACK = false keeps the scalar form: the one-cell kernels at n1 = 9 (FULL stiffness fp32: 161 registers at one
+// resident block) spill with the packed form and lose 5 points
+template <typename T, int N1, bool PACK = true>
 __device__ __forceinline__ void axpy_n(const T (&m)[N1], T x, T (&y)[N1])
 {
-  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2 && PACK)
   {
     const float2 xx = make_float2(x, x);
 #pragma unroll
@@ -150,10 +152,10 @@ __device__ __forceinline__ void axpy_n(const T (&m)[N1], T x, T (&y)[N1])
   }
 }
 // {r0, r1} = sum_p m[p] * {z0[p], z1[p]}: one table row against the same column of two cells
-template <typename T, int N1>
+template <typename T, int N1, bool PACK = true>
 __device__ __forceinline__ void dot2_n(const T (&m)[N1], const T (&z0)[N1], const T (&z1)[N1], T& r0, T& r1)
 {
-  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2 && PACK)
   {
     float2 acc = __fmul2_rn(make_float2(m[0], m[0]), make_float2(z0[0], z1[0]));
 #pragma unroll
@@ -190,11 +192,11 @@ __device__ __forceinline__ void contract_in_trip(const T* Ma, const T* Mb, int o
   {
     T m[N1];
     tab_run<T, N1>(Ma, off + u * LD, m);
-    axpy_n<T, N1>(m, xp[u], ya);
+    axpy_n<T, N1, N1 != 9>(m, xp[u], ya);
     if constexpr (DUAL)
     {
       tab_run<T, N1>(Mb, off + u * LD, m);
-      axpy_n<T, N1>(m, xp[u], yb);
+      axpy_n<T, N1, N1 != 9>(m, xp[u], yb);
     }
   }
 }
@@ -272,7 +274,7 @@ template <typename T, int N1>
 __device__ __forceinline__ void contract_out(const T (&MT)[N1 * tab_ld<N1>()], const T (&z)[N1], T* buf, int base, int stride)
 {
   constexpr int LD = tab_ld<N1>();
-  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2)
+  if constexpr (sizeof(T) == 4 && FEMTC_FFMA2 && N1 != 9)
   {
     // fp32: rows i, i+1 together.  MT[p + i*LD] = A(i,p); the pair {A(i,p), A(i+1,p)} is gathered from two rows of
     // the transposed table (constant-bank operands), z[p] is broadcast; lane results equal the scalar form's.
@@ -323,7 +325,7 @@ __device__ __forceinline__ void col_axpy(const T (&M)[N1 * tab_ld<N1>()], int p,
 {
   T m[N1];
   tab_run<T, N1>(M, p * tab_ld<N1>(), m);
-  axpy_n<T, N1>(m, f, y);
+  axpy_n<T, N1, N1 != 9>(m, f, y);
 }
 
 // ---- two cells per thread -------------------------------------------------------------------------------
@@ -1130,9 +1132,9 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
           T mrow[N1];
           tab_run<T, N1>(B.at, i0 * tab_ld<N1>(), mrow);
           if constexpr (FULL)
-            dot2_n<T, N1>(mrow, td, sa, w1, w2);
+            dot2_n<T, N1, N1 != 9>(mrow, td, sa, w1, w2);
           else
-            dot2_n<T, N1>(mrow, td, ta, w1, w2);
+            dot2_n<T, N1, N1 != 9>(mrow, td, ta, w1, w2);
         }
         mbar_wait(barG + 8 * c_slot, c_par);
         const int sh = SC::F32 ? ((my_par + i0 * (N2 & 1)) & 1) : 0;
