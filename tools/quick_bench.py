@@ -85,16 +85,26 @@ def sweep(a, ops, dtypes, degrees, modes):
                                 femtc.mass_operator(phi, U, W, G, cells, P)
                             else:
                                 femtc.stiffness_operator(phi, U, W, G, cells, P, mode=mode)
-                        for _ in range(a.warmup):
-                            run()
-                        torch.cuda.synchronize()
+                        # warm-up: at least `warmup` launches AND at least ~30 ms of them (a 20 us kernel launched three
+                        # times leaves the clocks where the previous configuration's idle gap put them); timed: at least
+                        # `reps` launches and ~20 ms
                         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         e0.record()
-                        for _ in range(a.reps):
+                        for _ in range(a.warmup):
                             run()
                         e1.record()
                         torch.cuda.synchronize()
-                        ms = e0.elapsed_time(e1) / a.reps
+                        per = max(e0.elapsed_time(e1) / a.warmup, 1e-3)
+                        for _ in range(min(2000, int(30.0 / per))):
+                            run()
+                        reps = max(a.reps, min(2000, int(20.0 / per)))
+                        torch.cuda.synchronize()
+                        e0.record()
+                        for _ in range(reps):
+                            run()
+                        e1.record()
+                        torch.cuda.synchronize()
+                        ms = e0.elapsed_time(e1) / reps
                         gdofs = cells * nd / ms / 1e6
                         gbs = gdofs * (2 + gw) * sz
                         print(f"{op:9s} {dt} P={P} mode={mode} variant={variant} cells={cells:8d} "
