@@ -1176,6 +1176,8 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         }
         // REF_EXACT: only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
         col_axpy(B.a, i0, f2, h2);                              // A0 f2
+        if constexpr (!PW)
+          staging_reads_done(); // the refill below is issued by this warp; PW hands over through a release-arrive
         __syncwarp(); // every lane is done with this slot: request the chunk NG ahead into it
         if constexpr (PW)
         {

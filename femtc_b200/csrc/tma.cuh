@@ -18,6 +18,22 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
 {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// Generic-proxy reads of a staging buffer followed by a bulk copy that refills it: when the values read are not yet
+// consumed (no store or barrier depends on them), nothing orders the reads before the async-proxy write, and a refill
+// served from L2 can overtake shared-memory loads still queued behind bank conflicts (measured: slab mass kernel,
+// fp32 n1 = 8, 48 of 399 launches wrong; tools/probe/repeat_probe.py).  Every reading lane calls this before the
+// __syncwarp() / barrier that precedes the refill; the CTA-scope fence waits for the lane's outstanding loads.
+// Not needed where the values are consumed first (a store or block barrier depends on them) or where the slot is
+// handed to a producer warp by mbarrier.arrive (release; the canonical consumer-release pattern).
+#ifndef FEMTC_REFILL_FENCE
+#define FEMTC_REFILL_FENCE 1
+#endif
+__device__ __forceinline__ void staging_reads_done()
+{
+#if FEMTC_REFILL_FENCE
+  __threadfence_block();
+#endif
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
