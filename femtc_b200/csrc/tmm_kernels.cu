@@ -250,12 +250,21 @@ long long run_tmm(int Tr, const T* I0, const T* I1, const T* I2, const T* dB, T*
   fill_tab<T, NA, NB>(M.i1, I1, Tr);
   fill_tab<T, NA, NB>(M.i2, I2, Tr);
   auto kernel = tmm_kernel<T, NA, NB>;
-  int bps = 0;
-  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PL::smem_bytes) != cudaSuccess ||
-      cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) != cudaSuccess ||
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, PL::NT, PL::smem_bytes) != cudaSuccess || bps < 1)
+  // planned once per shape (thread-safe static): the attribute calls and the occupancy query cost more host time
+  // than a small batch spends on the device
+  static const int bps = [&]() {
+    int b = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PL::smem_bytes) != cudaSuccess ||
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kernel, PL::NT, PL::smem_bytes) != cudaSuccess || b < 1)
+    {
+      (void)cudaGetLastError();
+      return 0;
+    }
+    return b;
+  }();
+  if (bps < 1)
   {
-    (void)cudaGetLastError();
     set_error("tmm kernel: launch planning failed");
     return -FEMTC_ERR_CUDA;
   }

@@ -6,6 +6,7 @@ One line per (Na, Nb): tensors/s, algorithmic GB/s = (Nb^3 + Na^3) sizeof(T) per
 import argparse
 import json
 import sys
+import time
 from pathlib import Path
 
 import numpy as np
@@ -33,13 +34,15 @@ def main():
         tdt, npdt, sz = (torch.float64, np.float64, 8) if dt == "f64" else (torch.float32, np.float32, 4)
         for shp in a.shapes.split(","):
             Na, Nb = (int(v) for v in shp.split(":"))
-            batch = a.batch
+            batch = max(a.batch, int(1.5e9 / ((Nb ** 3 + Na ** 3) * sz)))   # small shapes: time the device, not the launch
             I = [rng.random(Na * Nb).astype(npdt) for _ in range(3)]
             B = fill_uniform(torch.empty(batch * Nb ** 3, dtype=tdt, device="cuda"), 1, 1)
             A = torch.empty(batch * Na ** 3, dtype=tdt, device="cuda")
-            for _ in range(3):
-                femtc.apply_contractions(*I, B, A, Na, Nb, True, batch=batch)
-            torch.cuda.synchronize()
+            t0 = time.perf_counter()                       # at least 50 ms of warm-up: the SM clock has to ramp
+            while time.perf_counter() - t0 < 0.05:
+                for _ in range(5):
+                    femtc.apply_contractions(*I, B, A, Na, Nb, True, batch=batch)
+                torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for _ in range(a.reps):
