@@ -867,7 +867,7 @@ struct StiffCol
   static constexpr int piece_stride = up16(G::N2 * RB + (F32 ? 8 : 0));  // PW: one cell's plane (+ fp32 skew)
   static constexpr int slot_bytes = PW ? C * piece_stride : up16(32 * RB) + (F32 ? 32 * MAXP + 16 : 0);
   static constexpr int ring_bytes = (PW ? 1 : G::NWARPS) * NG * slot_bytes;
-  static constexpr int n_bars = PW ? 1 + 2 * NG : 1 + G::NWARPS * NG;
+  static constexpr int n_bars = PW ? 1 + 2 * NG : 1 + 2 * G::NWARPS * NG; // U, then `full` and `empty` per ring slot
   static constexpr int threads = G::NT + (PW ? 32 : 0);
   static constexpr int NE = G::viaC ? 4 : 3;
   static constexpr int off_u = 0;
@@ -905,8 +905,8 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   unsigned char* gRing = smem + SC::off_g + (PW ? 0 : warp * NG * SC::slot_bytes);
   const uint32_t barU = smem_u32(smem + SC::off_bar);
-  const uint32_t barG = barU + 8 + (PW ? 0 : warp * NG * 8);   // `full` barriers of the ring slots
-  const uint32_t barE = barG + 8 * NG;                            // PW: `empty` barriers
+  const uint32_t barG = barU + 8 + (PW ? 0 : warp * 2 * NG * 8); // `full` barriers of the ring slots
+  const uint32_t barE = barG + 8 * NG;                            // their `empty` barriers (PW: one arrival per compute warp)
   // the compute threads' block barrier (the producer warp never takes part in it)
   auto block_sync = [&]()
   {
@@ -986,7 +986,10 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
   else if (lane == 0)
   {
     for (int s = 0; s < NG; ++s)
+    {
       mbar_init(barG + 8 * s, npieces);
+      mbar_init(barE + 8 * s, FEMTC_RELEASE_LANES);
+    }
     fence_mbar_init();
   }
   __syncthreads();
@@ -1176,18 +1179,22 @@ stiffness_column_kernel(const __grid_constant__ TabAD<T, N1> B, const T* __restr
         }
         // REF_EXACT: only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
         col_axpy(B.a, i0, f2, h2);                              // A0 f2
-        if constexpr (!PW)
-          staging_reads_done(); // the refill below is issued by this warp; PW hands over through a release-arrive
-        __syncwarp(); // every lane is done with this slot: request the chunk NG ahead into it
+        // every lane is done with this slot: hand it back through its `empty` barrier (tma.cuh, rule 2) -- to the
+        // producer warp (PW), or to this warp's own issuing lanes, which then request the chunk NG ahead into it
         if constexpr (PW)
         {
+          __syncwarp();
           if (lane == 0)
             mbar_arrive(barE + 8 * c_slot);
         }
-        else if (i0 + NG < N1)
-          request_plane(i0 + NG, c_slot, g_tile);
-        else if (tn < ntiles)
-          request_plane(i0 + NG - N1, c_slot, g_tile + g_stride);
+        else
+        {
+          slot_release_and_acquire(barE + 8 * c_slot, c_par, lane);
+          if (i0 + NG < N1)
+            request_plane(i0 + NG, c_slot, g_tile);
+          else if (tn < ntiles)
+            request_plane(i0 + NG - N1, c_slot, g_tile + g_stride);
+        }
         if (++c_slot == NG)
         {
           c_slot = 0;

@@ -18,22 +18,21 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
 {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// Generic-proxy reads of a staging buffer followed by a bulk copy that refills it: when the values read are not yet
-// consumed (no store or barrier depends on them), nothing orders the reads before the async-proxy write, and a refill
-// served from L2 can overtake shared-memory loads still queued behind bank conflicts (measured: slab mass kernel,
-// fp32 n1 = 8, 48 of 399 launches wrong; tools/probe/repeat_probe.py).  Every reading lane calls this before the
-// __syncwarp() / barrier that precedes the refill; the CTA-scope fence waits for the lane's outstanding loads.
-// Not needed where the values are consumed first (a store or block barrier depends on them) or where the slot is
-// handed to a producer warp by mbarrier.arrive (release; the canonical consumer-release pattern).
-#ifndef FEMTC_REFILL_FENCE
-#define FEMTC_REFILL_FENCE 1
+// Generic-proxy reads of a staging buffer followed by a bulk copy (async proxy) that refills it: a write-after-read
+// hazard that __syncwarp() and a CTA fence do not close (measured in round 1: slab mass kernel, fp32 n1 = 8, 48 of 399
+// launches wrong without a fence, ~1 in 500 with one; tools/probe/repeat_probe.py) -- a refill served from L2 can
+// overtake shared-memory loads still queued behind bank conflicts.  Two rules close it, neither depends on where the
+// compiler places instructions:
+//  (1) buffers whose values go straight into a shared-memory store or a block barrier (U, detJ staging) are refilled
+//      only after that store / barrier: the store cannot issue before the loads have returned;
+//  (2) ring slots whose values are consumed into registers only (the geometry rings) are handed back through a
+//      per-slot `empty` mbarrier, the consumer-release pattern of every TMA pipeline: each reading lane executes
+//      mbarrier.arrive (release.cta: the lane's prior shared-memory reads are performed before the arrival, and the
+//      arrival is queued behind them in the same in-order shared-memory pipe), and the lanes that issue the refill
+//      wait (acquire) for the phase, i.e. for all arrivals, before cp.async.bulk.  slot_release_and_acquire() below.
+#ifndef FEMTC_RELEASE_LANES
+#define FEMTC_RELEASE_LANES 32 // arrivals per warp on an `empty` barrier (32: every reading lane; 1: lane 0 after __syncwarp, A/B only)
 #endif
-__device__ __forceinline__ void staging_reads_done()
-{
-#if FEMTC_REFILL_FENCE
-  __threadfence_block();
-#endif
-}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -50,6 +49,20 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
                "}" ::"r"(bar),
                "r"(parity)
                : "memory");
+}
+// Every lane of a (converged) warp: "my reads of this ring slot are done", then wait until all lanes have said so.
+// On return the calling lane may refill the slot with a bulk copy.  `parity` = (number of earlier uses of the slot) & 1.
+__device__ __forceinline__ void slot_release_and_acquire(uint32_t bar_empty, uint32_t parity, int lane)
+{
+#if FEMTC_RELEASE_LANES == 32
+  (void)lane;
+  mbar_arrive(bar_empty);
+#else
+  __syncwarp();
+  if (lane == 0)
+    mbar_arrive(bar_empty);
+#endif
+  mbar_wait(bar_empty, parity);
 }
 // global -> shared bulk copy (TMA), completion signalled on an mbarrier
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)

@@ -188,3 +188,31 @@ def test_reference_drivers_build_unchanged():
     assert r.returncode == 0, r.stderr
     for name in ("test_gemm", "test_micro", "bench_mass", "bench_stiffness"):
         assert (ROOT / "compat" / "_bin" / name).exists()
+
+
+def test_nvtx_ranges_open_and_close_around_the_operator_entry_points(tmp_path):
+    """NVTX ranges stand in for the reference's LIKWID marker regions "mass"+typeid(T).name()
+    (bench_mass.cpp:41-47,94,108-109).  A minimal NVTX injection library (tests/nvtx_probe, what a profiler installs
+    through NVTX_INJECTION64_PATH) records the pushes and pops of a process that calls the four host-pointer operator
+    entry points; the ranges open before any CUDA work, so this runs with or without a GPU."""
+    import os
+    import sys
+    so = tmp_path / "libnvtx_probe.so"
+    subprocess.run(["gcc", "-shared", "-fPIC", "-O1", "-o", str(so), str(ROOT / "tests" / "nvtx_probe" / "nvtx_inject.c")],
+                   check=True)
+    log = tmp_path / "nvtx.log"
+    code = (
+        "import numpy as np, femtc_b200 as f\n"
+        "from femtc_b200 import _lib\n"
+        "for dt, s in ((np.float64, 'f64'), (np.float32, 'f32')):\n"
+        "    phi, U, W, G = np.ones(32, dt), np.ones(64, dt), np.zeros(64, dt), np.ones(384, dt)\n"
+        "    p = lambda a: a.ctypes.data\n"
+        "    getattr(_lib.lib, 'femtc_mass_apply_' + s)(p(phi), 32, p(U), p(W), p(U), 1, 3, 0, 0, 0)\n"
+        "    getattr(_lib.lib, 'femtc_stiffness_apply_' + s)(p(phi), 32, p(U), p(W), p(G), 1, 3, 0, 0, 0, 0)\n")
+    env = dict(os.environ, NVTX_INJECTION64_PATH=str(so), FEMTC_NVTX_LOG=str(log), PYTHONPATH=str(ROOT))
+    subprocess.run([sys.executable, "-c", code], check=True, env=env, cwd=str(ROOT))
+    lines = log.read_text().split("\n")
+    pushes = [l.split(" ", 1)[1] for l in lines if l.startswith("push ")]
+    for name in ("massd", "stiffnessd", "massf", "stiffnessf"):
+        assert name in pushes, (name, pushes)
+    assert sum(l.startswith("pop") for l in lines) == len(pushes)
