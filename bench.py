@@ -19,6 +19,14 @@ A step is one operator application over the whole batch.  One JSON line is print
             measured kernel time, against the measured copy bandwidth in MEASURED_PEAKS.json.
   cpu_baseline   the UNMODIFIED reference (oracle/_ref, -Ofast) on the host cores, rank 0, N = 1.
 
+  sweep     (N = 1) BASELINE config 3 under this run's clock: mass / stiffness REF_EXACT / stiffness FULL x
+            P = 1..8 x fp32 / fp64 at 1 M cells = 48 entries, each with GDoF/s (min / median / max over five
+            placements of U, geometry, W inside one arena), fraction of the measured HBM peak, the kernel family
+            that served it, a clocks record for its own window and a spot check of three regenerated 40-cell
+            ranges (first / middle / last) against the CPU oracle.
+  strong    BASELINE config 5: stiffness P = 4 fp64, 64 M cells in total partitioned over the N GPUs (resident
+            chunks), spot checks at chunk boundaries, clocks over the whole leg.
+
 --impl reference times only that CPU reference, with every host thread, on the same workload.
 """
 from __future__ import annotations
@@ -59,6 +67,13 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the 48-entry degree sweep (N = 1 only)")
+    ap.add_argument("--sweep-cells", type=int, default=1_000_000)
+    ap.add_argument("--sweep-filter", default="", help="development: only entries whose name contains this")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (BASELINE config 5)")
+    ap.add_argument("--strong-cells", type=int, default=64_000_000)
+    ap.add_argument("--strong-degree", type=int, default=4)
+    ap.add_argument("--strong-steps", type=int, default=3)
     return ap.parse_args()
 
 
@@ -67,6 +82,18 @@ def workload_name(a):
     return (f"{'bench_stiffness: Laplace stiffness' if a.op == 'stiffness' else 'bench_mass: mass'} action, "
             f"degree-{a.degree} hexahedra, {'fp64' if a.dtype == 'f64' else 'fp32'}, {a.cells} cells per GPU, "
             f"U + {geom} -> W, synthetic uniform [0,1) inputs")
+
+
+def config_dict(a, world: int):
+    """The workload both arms are quoted on (the reference arm times a bounded sample of it and says so in
+    cpu_baseline.sample); identical in both arms' lines."""
+    nd, gw, size = (a.degree + 1) ** 3, OPS[a.op], 8 if a.dtype == "f64" else 4
+    return {"workload": workload_name(a), "op": a.op, "degree": a.degree, "mode": a.mode, "cells_per_gpu": a.cells,
+            "dofs_per_step": world * a.cells * nd,
+            "parallelism": f"cells partitioned over {world} GPU(s), no halo; one 4-double checksum all-gather (NCCL) "
+                           "at the end of the timed region",
+            "placement": "U | geometry | W back to back in one device allocation",
+            "l2": f"no flush needed: each step streams {a.cells * nd * (2 + gw) * size / 1e9:.2f} GB per GPU, 126 MB L2"}
 
 
 def peaks():
@@ -107,7 +134,7 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
 
     def __exit__(self, *exc):
         if self.proc:
@@ -115,10 +142,13 @@ class ClockSampler:
             self.proc.terminate()
             self.thread.join(timeout=2)
 
-    def summary(self):
+    def summary(self, t0: float | None = None, t1: float | None = None):
+        """all samples, or those received in the wall-clock window [t0, t1] (+ one sampling period)"""
         sm, mx, pw, reasons = [], [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for row in self.rows:
+        for t, row in list(self.rows):
+            if t0 is not None and not (t0 <= t <= t1 + 0.06):
+                continue
             f = [x.strip() for x in row.split(",")]
             if len(f) < 7:
                 continue
@@ -132,34 +162,60 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         busy = [s for s, p in zip(sm, pw) if p >= 0.5 * max(pw)] or sm
-        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
-                "reasons": sorted(reasons), "samples": len(sm),
-                "window": "timed region plus ~1 s of the same step repeated right after it"}
+        out = {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+               "reasons": sorted(reasons), "samples": len(sm)}
+        if t0 is None:
+            out["window"] = "timed region plus ~1 s of the same step repeated right after it"
+        return out
 
 
 # ------------------------------------------------------------------------------------------------------
 # CPU reference (oracle/_ref = the unmodified reference headers, -Ofast, widest ISA the host supports)
 # ------------------------------------------------------------------------------------------------------
-def cpu_reference_rate(a, cells: int, workers: int, reps: int, warm: int = 1, want_output: int = 0):
+def cpu_reference_rate(a, cells: int, workers: int, reps: int, warm: int = 1, want_output: int = 0, triple=None):
     """GDoF/s of the reference's own CPU kernel (oracle/_ref) with `workers` processes on disjoint
     cell ranges of the same synthetic inputs; see oracle/cpu_bench.py."""
     from oracle import cpu_bench
     return cpu_bench.run(a.op, a.degree, np.float64 if a.dtype == "f64" else np.float32, cells, workers, reps,
-                         warm, want_output)
+                         warm, want_output, triple)
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def cpu_tuning(a):
+    """the reference's knob sweep on ONE core at Ndofs = 10^6 (run.sh:9-23), six loop
+    orders x three (Mb, Nb) pairs, best kept.  None where the tuning library does not cover this degree."""
+    from oracle import cpu_bench
+    t = cpu_bench.tune(a.op, a.degree, np.float64 if a.dtype == "f64" else np.float32)
+    if t is None:
+        return None, None
+    return t["best"], {"one_core_best": t["best_name"], "one_core_best_gdofs": t["rate"],
+                       "one_core_table_gdofs": {k: round(v, 5) for k, v in t["table"].items()},
+                       "protocol": "1 core, Ndofs = 1e6, 10 repetitions, mean of the last 5 (bench_mass.cpp:95-106); "
+                                   "orders ijk..kji x (Mb,Nb) in {(0,0),(4,8),(8,16)} (run.sh:13-23)"}
 
 
 def run_reference(a, rank: int):
     if rank != 0:
         return
     workers = os.cpu_count() or 1
+    triple, tuning = cpu_tuning(a)
     # bounded sample: shrink the batch until one pass takes about a second on this host
     cells = a.cells
-    probe = cpu_reference_rate(a, min(cells, 16384 * workers), workers, reps=1, warm=0)
+    probe = cpu_reference_rate(a, min(cells, 16384 * workers), workers, reps=1, warm=0, triple=triple)
     est = cells / min(cells, 16384 * workers) * probe["sec"]
     while est > 1.5 and cells > 16384 * workers:
         cells //= 2
         est /= 2
-    res = cpu_reference_rate(a, cells, workers, reps=a.steps, warm=max(1, min(a.warmup, 3)))
+    res = cpu_reference_rate(a, cells, workers, reps=a.steps, warm=max(1, min(a.warmup, 3)), triple=triple)
     rate, sec, kind, desc = res["rate"], res["sec"], res["kind"], res["desc"]
     threads = workers
     nd = (a.degree + 1) ** 3
@@ -167,9 +223,12 @@ def run_reference(a, rank: int):
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "GDoF/s", "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": a.dtype, "data": "synthetic",
-        "config": {"workload": workload_name(a), "op": a.op, "degree": a.degree, "mode": a.mode,
-                   "cells_per_step": cells, "dofs_per_step": cells * nd},
-        "cpu_baseline": {"value": rate, "unit": "GDoF/s", "cores": threads, "kind": kind, "sample": desc},
+        "config": config_dict(a, a.gpus),
+        "sample_cells_per_step": cells, "sample_dofs_per_step": cells * nd,
+        "note": "a rate: the CPU reference is timed on a bounded sample of ONE GPU's batch whatever --gpus says "
+                "(the repo arm at N GPUs processes N batches per step)",
+        "cpu_baseline": {"value": rate, "unit": "GDoF/s", "cores": threads, "kind": kind, "sample": desc,
+                         "cpu": cpu_model(), "tuning": tuning},
         "e2e": {"value": rate, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -177,31 +236,46 @@ def run_reference(a, rank: int):
 
 
 # ------------------------------------------------------------------------------------------------------
-def run_strong(a, rank: int, local_rank: int, world: int):
-    """BASELINE config 5: a fixed global batch (--total-cells) partitioned over the GPUs, no halo.  A rank holds
-    at most --resident-gb of fields; a larger share is swept in chunks (inputs regenerated on the device between
-    chunks, outside the timed spans).  Timed: the operator launches only (CUDA events per chunk, summed; max over
-    ranks).  The one collective is the 4-double checksum all-gather at the end."""
+def spot_check(femtc_mod, oracle_mod, W_dev, op, P, ndt, mode, phi, ranges, nd):
+    """max |w - ref| / max |ref| over regenerated cell ranges: [(first global cell, cells, offset of that cell in W_dev)].
+    The oracle (CPU restatement, pinned to the compiled reference) is the checker here, after the timing."""
+    o = oracle_mod["o"]
+    worst = 0.0
+    for c0, n, off in ranges:
+        _, u, g = oracle_mod["splitmix"](o, op, P, n, ndt, 1, cell0=c0)
+        rc, ref = (o.mass(phi, u, g, P) if op == "mass" else o.stiffness(phi, u, g, P, mode=mode))
+        assert rc == 0
+        got = W_dev[off * nd:(off + n) * nd].cpu().numpy().astype(np.float64)
+        ref = ref.astype(np.float64)
+        worst = max(worst, float(np.abs(got - ref).max() / np.abs(ref).max()))
+    return worst
+
+
+def load_oracle():
+    from oracle import Oracle, splitmix
+    return {"o": Oracle(), "splitmix": splitmix}
+
+
+def strong_leg(a, rank, local_rank, world, dev, *, op, degree, dtype, mode_name, total_cells, steps, warm, resident_gb):
+    """BASELINE config 5: a fixed global batch partitioned over the GPUs, no halo.  A rank holds at most
+    `resident_gb` of fields; a larger share is swept in chunks (inputs regenerated on the device between chunks,
+    outside the timed spans).  Timed: the operator launches only (CUDA events per chunk, summed; max over ranks).
+    The one collective is the 4-double checksum all-gather at the end.  Every chunk's first and last 40 cells are
+    regenerated on the host and compared with the oracle.  Returns the result dict on rank 0, None elsewhere."""
     import torch
     import torch.distributed as dist
 
     import femtc_b200 as femtc
-    from femtc_b200 import _lib
     from femtc_b200.distributed import combine_checksums, device_checksum, fill_uniform, partition
 
-    torch.cuda.set_device(local_rank)
-    _lib.check(_lib.lib.femtc_set_device(local_rank))
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    P, nd, gw = a.degree, (a.degree + 1) ** 3, OPS[a.op]
-    tdt = torch.float64 if a.dtype == "f64" else torch.float32
-    ndt = np.float64 if a.dtype == "f64" else np.float32
-    size = 8 if a.dtype == "f64" else 4
-    mode = femtc.FULL if a.mode == "full" else femtc.REF_EXACT
-    lo, hi = partition(a.total_cells, rank, world)
+    P, nd, gw = degree, (degree + 1) ** 3, OPS[op]
+    tdt = torch.float64 if dtype == "f64" else torch.float32
+    ndt = np.float64 if dtype == "f64" else np.float32
+    size = 8 if dtype == "f64" else 4
+    mode = femtc.FULL if mode_name == "full" else femtc.REF_EXACT
+    lo, hi = partition(total_cells, rank, world)
     bytes_per_cell = nd * (2 + gw) * size
-    chunk = max(32, int(a.resident_gb * 1e9 / bytes_per_cell) // 32 * 32)
+    chunk = max(32, int(resident_gb * 1e9 / bytes_per_cell) // 32 * 32)
     chunk = min(chunk, hi - lo)
     n2 = (P + 1) ** 2
     phi = fill_uniform(torch.empty(2 * n2, dtype=tdt, device=dev), 1, 0, 0).cpu().numpy().astype(ndt)
@@ -211,15 +285,16 @@ def run_strong(a, rank: int, local_rank: int, world: int):
     nU, nG = chunk * nd, chunk * nd * gw
     arena = torch.empty(up(nU) + up(nG) + up(nU), dtype=tdt, device=dev)
     U, G, W = arena[:nU], arena[up(nU):up(nU) + nG], arena[up(nU) + up(nG):up(nU) + up(nG) + nU]
+    orc = load_oracle()
 
     def apply(n):
-        rc = (femtc.mass_operator(phi, U, W, G, n, P) if a.op == "mass"
+        rc = (femtc.mass_operator(phi, U, W, G, n, P) if op == "mass"
               else femtc.stiffness_operator(phi, U, W, G, n, P, mode=mode))
         assert rc == 0
 
     def sweep(reps_per_chunk, timed):
-        """one pass over the rank's cells; returns (kernel ms, checksum partials)"""
-        ms, parts = 0.0, []
+        """one pass over the rank's cells; returns (kernel ms, checksum partials, worst spot-check error)"""
+        ms, parts, worst = 0.0, [], 0.0
         for c0 in range(lo, hi, chunk):
             n = min(chunk, hi - c0)
             fill_uniform(U[:n * nd], 1, 1, c0 * nd)
@@ -234,48 +309,218 @@ def run_strong(a, rank: int, local_rank: int, world: int):
             ms += e0.elapsed_time(e1) / reps_per_chunk
             if timed:
                 parts.append(device_checksum(W[:n * nd]).cpu().numpy())
-        return ms, parts
+                k = min(40, n)
+                worst = max(worst, spot_check(femtc, orc, W, op, P, ndt, mode, phi,
+                                              [(c0, k, 0), (c0 + n - k, k, n - k)], nd))
+        return ms, parts, worst
 
-    sweep(max(1, min(a.warmup, 3)), False)
+    sweep(warm, False)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     launches0 = femtc.get_option("launches")
     with ClockSampler(local_rank) as clocks:
-        ms, parts = sweep(a.steps, True)
+        ms, parts, worst = sweep(steps, True)
+        # keep the same load up for a moment so that a short leg still collects clock samples
+        t_end = time.perf_counter() + 0.4
+        while time.perf_counter() < t_end:
+            apply(min(chunk, hi - lo))
+            torch.cuda.synchronize()
     launches = femtc.get_option("launches") - launches0
     loc = np.array([sum(p[0] for p in parts), sum(p[1] for p in parts), max(p[2] for p in parts), sum(p[3] for p in parts)])
     loc_t = torch.tensor(loc, dtype=torch.float64, device=dev)
     glob = combine_checksums(loc_t) if world > 1 else loc_t
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, worst], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = t.item()
+    ms_step, worst = t[0].item(), t[1].item()
+    del arena, U, G, W
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    peak, peak_src = peaks()
+    dofs = total_cells * nd
+    achieved = (hi - lo) * nd * (2 + gw) * size / (ms_step * 1e-3) / 1e9
+    cs = [float(x) for x in glob.cpu().numpy()]
+    tol = 1e-12 if dtype == "f64" else 1e-5
+    return {
+        "value": dofs / ms_step / 1e6, "unit": "GDoF/s", "scaling": "strong", "n_gpus": world, "steps": steps,
+        "warmup": warm, "ms_per_step": ms_step, "dtype": dtype,
+        "config": {"workload": f"{op} action degree {P}, {dtype}, {total_cells} cells in total partitioned over "
+                               f"{world} B200" + (" with NCCL checksum reduction" if world > 1 else ""),
+                   "op": op, "degree": P, "mode": mode_name, "total_cells": total_cells, "cells_this_rank": hi - lo,
+                   "resident_chunk_cells": chunk, "chunks_per_rank": -(-(hi - lo) // chunk), "dofs_per_step": dofs,
+                   "timed": "operator launches only, CUDA events per resident chunk summed, max over ranks; inputs are "
+                            "regenerated on the device between chunks outside the timed spans",
+                   "l2": f"no flush needed: every chunk streams {chunk * bytes_per_cell / 1e9:.1f} GB"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_dof": (2 + gw) * size},
+        "gpu_launches": int(launches), "clocks": clocks.summary(),
+        "parity": {"max_rel_err": worst, "tol": tol, "ok": bool(worst <= tol),
+                   "checked": "first and last 40 cells of every resident chunk on every rank vs the CPU oracle"},
+        "checksum": {"sum": cs[0], "sum_sq": cs[1], "max_abs": cs[2], "n": cs[3]},
+    }
+
+
+def run_strong(a, rank: int, local_rank: int, world: int):
+    """`--total-cells N`: only the strong-scaling leg, printed as the line."""
+    import torch
+    import torch.distributed as dist
+
+    from femtc_b200 import _lib
+
+    torch.cuda.set_device(local_rank)
+    _lib.check(_lib.lib.femtc_set_device(local_rank))
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    res = strong_leg(a, rank, local_rank, world, dev, op=a.op, degree=a.degree, dtype=a.dtype, mode_name=a.mode,
+                     total_cells=a.total_cells, steps=a.steps, warm=max(1, min(a.warmup, 3)), resident_gb=a.resident_gb)
     if rank == 0:
-        peak, peak_src = peaks()
-        dofs = a.total_cells * nd
-        achieved = (hi - lo) * nd * (2 + gw) * size / (ms_step * 1e-3) / 1e9
-        cs = [float(x) for x in glob.cpu().numpy()]
-        print(json.dumps({
-            "metric": METRIC, "value": dofs / ms_step / 1e6, "unit": "GDoF/s", "n_gpus": world, "steps": a.steps,
-            "warmup": max(1, min(a.warmup, 3)), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
-            "config": {"workload": f"stiffness action degree {P}, {a.dtype}, {a.total_cells} cells in total partitioned over "
-                                   f"{world} B200 with NCCL checksum reduction" if a.op == "stiffness" else
-                                   f"mass action degree {P}, {a.dtype}, {a.total_cells} cells in total over {world} B200",
-                       "op": a.op, "degree": P, "mode": a.mode, "total_cells": a.total_cells, "cells_this_rank": hi - lo,
-                       "resident_chunk_cells": chunk, "chunks_per_rank": -(-(hi - lo) // chunk), "dofs_per_step": dofs,
-                       "timed": "operator launches only, CUDA events per resident chunk summed, max over ranks; inputs are "
-                                "regenerated on the device between chunks outside the timed spans",
-                       "l2": f"no flush needed: every chunk streams {chunk * bytes_per_cell / 1e9:.1f} GB"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_dof": (2 + gw) * size},
-            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(),
-            "checksum": {"sum": cs[0], "sum_sq": cs[1], "max_abs": cs[2], "n": cs[3]},
-        }), flush=True)
+        line = {"metric": METRIC, "value": res["value"], "unit": "GDoF/s", "n_gpus": world, "steps": a.steps,
+                "warmup": res["warmup"], "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic", "e2e": None}
+        line.update({k: res[k] for k in ("config", "roofline", "gpu_launches", "clocks", "parity", "checksum")})
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------------
+# BASELINE config 3: the degree sweep, under this run's clock
+# ------------------------------------------------------------------------------------------------------
+FAMILY = {0: "generic", 1: "slab", 2: "cell", 3: "column", 4: "tensor-core"}
+MIB = 1 << 20
+# five placements of the three fields inside one arena: (first byte, gap between fields, order)
+PLACEMENTS = ((0, 0, "UGW"), (34 * MIB + 768, 6 * MIB + 1280, "UGW"), (10 * MIB, 0, "WUG"),
+              (0, 14 * MIB + 256, "GWU"), (82 * MIB, 13 * 65536, "UGW"))
+
+
+def place(i: int, bU: int, bG: int):
+    base, gap, order = PLACEMENTS[i]
+    size = {"U": bU, "G": bG, "W": bU}
+    off, cur = {}, base
+    for f in order:
+        off[f] = cur
+        cur = (cur + size[f] + 255) // 256 * 256 + gap
+    return off, cur
+
+
+def run_sweep(a, dev, local_rank):
+    """48 entries: (mass, stiffness REF_EXACT, stiffness FULL) x P = 1..8 x (fp64, fp32), a.sweep_cells cells each."""
+    import torch
+
+    import femtc_b200 as femtc
+    from femtc_b200 import _lib
+    from femtc_b200.distributed import fill_uniform
+
+    cells = a.sweep_cells
+    peak, _ = peaks()
+    orc = load_oracle()
+    stream = torch.cuda.current_stream().cuda_stream
+    todo = [(op, mode_name, dtype, P, f"{op}{'_full' if mode_name == 'full' else ''}_P{P}_{dtype}")
+            for op, mode_name in (("mass", "ref_exact"), ("stiffness", "ref_exact"), ("stiffness", "full"))
+            for dtype in ("f64", "f32") for P in range(1, 9)]
+    todo = [t for t in todo if a.sweep_filter in t[4]]
+    need = 0
+    for op, _, dtype, P, _ in todo:
+        b = cells * (P + 1) ** 3 * (8 if dtype == "f64" else 4)
+        need = max(need, max(place(i, b, b * OPS[op])[1] for i in range(len(PLACEMENTS))))
+    arena = torch.empty(need, dtype=torch.uint8, device=dev)
+    entries = []
+    with ClockSampler(local_rank) as clocks:
+        for op, mode_name, dtype, P, name in todo:
+            nd, gw, n2 = (P + 1) ** 3, OPS[op], (P + 1) ** 2
+            tdt = torch.float64 if dtype == "f64" else torch.float32
+            ndt = np.float64 if dtype == "f64" else np.float32
+            size = 8 if dtype == "f64" else 4
+            mode = femtc.FULL if mode_name == "full" else femtc.REF_EXACT
+            phi = fill_uniform(torch.empty(2 * n2, dtype=tdt, device=dev), 1, 0, 0).cpu().numpy().astype(ndt)
+            bU, bG = cells * nd * size, cells * nd * gw * size
+            fn = getattr(_lib.lib, f"femtc_{op}_apply_device_{dtype}")
+            t_entry0 = time.time()
+            ms_all = []
+            for i in range(len(PLACEMENTS)):
+                off, _ = place(i, bU, bG)
+                U = arena[off["U"]:off["U"] + bU].view(tdt)
+                G = arena[off["G"]:off["G"] + bG].view(tdt)
+                W = arena[off["W"]:off["W"] + bU].view(tdt)
+                fill_uniform(U, 1, 1, 0)
+                fill_uniform(G, 1, 2, 0)
+                # the C ABI entry itself, arguments prepared once: at P = 1 the kernel lasts ~20 us and the
+                # Python wrapper's checks would be part of the measurement
+                args = [phi.ctypes.data, phi.size, U.data_ptr(), W.data_ptr(), G.data_ptr(), cells, P]
+                args += [mode, stream] if op == "stiffness" else [stream]
+
+                def launch(reps):
+                    for _ in range(reps):
+                        rc = fn(*args)
+                        if rc:
+                            _lib.check(rc)
+                launch(2)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); launch(1); e1.record()
+                torch.cuda.synchronize()
+                est = max(e0.elapsed_time(e1), 1e-3)
+                launch(max(3, int(20.0 / est)))  # >= 20 ms of warm-up: the clocks have ramped
+                reps = min(4000, max(5, int(40.0 / est)))
+                torch.cuda.synchronize()
+                e0.record(); launch(reps); e1.record()
+                torch.cuda.synchronize()
+                ms_all.append(e0.elapsed_time(e1) / reps)
+            t_entry1 = time.time()
+            err = spot_check(femtc, orc, W, op, P, ndt, mode, phi,
+                             [(0, 40, 0), (cells // 2 + 3, 40, cells // 2 + 3), (cells - 40, 40, cells - 40)], nd)
+            tol = 1e-12 if dtype == "f64" else 1e-5
+            info = femtc.kernel_info(op, size, P, mode)
+            rate = lambda ms: cells * nd / ms / 1e6
+            gbs = lambda ms: cells * nd * (2 + gw) * size / (ms * 1e-3) / 1e9
+            med = float(np.median(ms_all))
+            entries.append({
+                "name": name, "op": op, "mode": mode_name, "degree": P, "dtype": dtype, "cells": cells,
+                "gdofs": {"min": rate(max(ms_all)), "median": rate(med), "max": rate(min(ms_all))},
+                "ms": {"min": min(ms_all), "median": med, "max": max(ms_all), "per_placement": ms_all},
+                "wall_s": t_entry1 - t_entry0,
+                "achieved_gbs": gbs(med), "frac": gbs(med) / peak, "frac_min": gbs(max(ms_all)) / peak,
+                "frac_max": gbs(min(ms_all)) / peak, "frac_of_nominal_8TBs": gbs(med) / 8000.0,
+                "placements": len(ms_all), "family": FAMILY.get(info["family"], "?"),
+                "kernel": {k: info[k] for k in ("cells_per_tile", "threads", "smem_bytes", "blocks_per_sm", "regs", "detail")},
+                "clocks": clocks.summary(t_entry0, t_entry1),
+                "max_rel_err": err, "tol": tol, "parity_ok": bool(err <= tol)})
+    del arena
+    torch.cuda.empty_cache()
+    return entries
+
+
+def stream_peaks(dev):
+    """Read-dominated streaming peaks measured now with the library's probe kernel (reads : 1 write of 16-byte words
+    with no arithmetic to speak of): the denominators that match the operators' traffic mix.  GB/s, best of 5."""
+    import torch
+
+    from femtc_b200 import _lib
+
+    per = 512 * MIB
+    src = torch.empty(7 * per, dtype=torch.uint8, device=dev).zero_()
+    dst = torch.empty(per, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    out = {}
+    for reads in (1, 2, 7):
+        best = 0.0
+        for rep in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(4):
+                _lib.check(_lib.lib.femtc_stream_probe_device(src.data_ptr(), dst.data_ptr(), per, reads, stream))
+            e1.record()
+            torch.cuda.synchronize()
+            if rep:
+                best = max(best, 4 * (reads + 1) * per / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+        out[f"{reads}:1"] = best
+    del src, dst
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_ours(a, rank: int, local_rank: int, world: int):
@@ -400,6 +645,32 @@ def run_ours(a, rank: int, local_rank: int, world: int):
                "h2d_bytes_per_step": int(cells * nd * (1 + gw) * size), "d2h_bytes_per_step": int(cells * nd * size),
                "ms_per_step": sec.item() * 1e3, "steps": a.e2e_steps,
                "api": f"femtc_{a.op}_apply_{a.dtype} (host pointers, pinned memory)"}
+        # The bound of that figure: the same pinned buffers moved by bare cudaMemcpyAsync, H2D (U, geometry) on one
+        # stream and D2H (W) on another, no kernel.  e2e.ms_per_step / this = how close the pipeline is to the link.
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        def copies():
+            with torch.cuda.stream(s_in):
+                U.copy_(hU, non_blocking=True)
+                G.copy_(hG, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                hW.copy_(W, non_blocking=True)
+            s_in.synchronize()
+            s_out.synchronize()
+        torch.cuda.synchronize()
+        copies()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.e2e_steps):
+            copies()
+        csec = torch.tensor([(time.perf_counter() - t0) / a.e2e_steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(csec, op=dist.ReduceOp.MAX)
+        e2e["copy_bound"] = {"ms_per_step": csec.item() * 1e3,
+                             "h2d_gbs": e2e["h2d_bytes_per_step"] / csec.item() / 1e9,
+                             "value_at_bound": dofs_step / csec.item() / 1e9, "unit": "GDoF/s",
+                             "pipeline_efficiency": csec.item() / sec.item(),
+                             "what": "same pinned buffers, cudaMemcpyAsync H2D (U, geometry) || D2H (W), no kernel; "
+                                     "max over ranks"}
         # Same metric with the geometry held by an operator handle (femtc_operator_*: detJ / G uploaded
         # once at set-up, as a solver would; the reference's own drivers re-apply the operator to the same
         # arrays, bench_stiffness.cpp:95-105).  Per step only U travels in and W out.  Reported beside the
@@ -440,6 +711,21 @@ def run_ours(a, rank: int, local_rank: int, world: int):
         other = {"mode": "full" if om == femtc.FULL else "ref_exact", "value": cells * nd / (k0.elapsed_time(k1) / 10) / 1e6,
                  "unit": "GDoF/s per GPU"}
 
+    # ---- free the headline fields, then the other BASELINE configurations under the same clock ----------------------
+    del arena, U, G, W
+    torch.cuda.empty_cache()
+    femtc_release = _lib.lib.femtc_release_cache
+    femtc_release()
+    strong = None
+    if not a.no_strong:
+        strong = strong_leg(a, rank, local_rank, world, dev, op="stiffness", degree=a.strong_degree, dtype="f64",
+                            mode_name="ref_exact", total_cells=a.strong_cells, steps=a.strong_steps, warm=1,
+                            resident_gb=a.resident_gb)
+    sweep = speaks = None
+    if world == 1 and not a.no_sweep:
+        speaks = stream_peaks(dev)
+        sweep = run_sweep(a, dev, local_rank)
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -453,11 +739,7 @@ def run_ours(a, rank: int, local_rank: int, world: int):
         "metric": METRIC, "value": value, "unit": "GDoF/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": a.dtype, "data": "synthetic",
-        "config": {"workload": workload_name(a), "op": a.op, "degree": P, "mode": a.mode, "cells_per_gpu": cells,
-                   "dofs_per_step": dofs_step, "parallelism": f"cells partitioned over {world} GPU(s), no halo; "
-                   "one 4-double checksum all-gather (NCCL) at the end of the timed region",
-                   "placement": "U | geometry | W back to back in one device allocation",
-                   "l2": f"no flush needed: each step streams {cells * nd * bytes_per_dof / 1e9:.2f} GB per GPU, 126 MB L2"},
+        "config": config_dict(a, world),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(a), "peak_source": peak_src,
                      "algorithmic_bytes_per_dof": bytes_per_dof, "kernel_ms": ms_kernel,
@@ -470,14 +752,39 @@ def run_ours(a, rank: int, local_rank: int, world: int):
     }
     if other:
         line["other_mode"] = other
+    if speaks:
+        mix = "7:1" if a.op == "stiffness" else "2:1"
+        line["roofline"]["stream_peaks_gbs"] = speaks
+        line["roofline"]["frac_of_stream_peak"] = achieved / speaks[mix]
+        line["roofline"]["stream_peak_note"] = (f"read-dominated streaming kernel of the library, measured in this run; this "
+                                                f"operator's mix is {mix} reads:writes, the MEASURED_PEAKS copy is 1:1")
+    if strong:
+        line["strong"] = strong
+    if sweep is not None:
+        line["sweep"] = sweep
+        ok = [e for e in sweep if e["parity_ok"]]
+        low = [e for e in sweep if e["degree"] <= 4 and e["mode"] == "ref_exact"]
+        line["sweep_summary"] = {
+            "entries": len(sweep), "parity_ok": len(ok), "cells": a.sweep_cells,
+            "min_median_frac_degree_le4_mass_and_ref_exact": min((e["frac"] for e in low), default=None),
+            "median_frac_all": float(np.median([e["frac"] for e in sweep])) if sweep else None,
+            "peak": peak, "peak_source": peak_src,
+            "timing": "per entry and placement: >= 20 ms warm-up, then >= 40 ms (>= 5 launches) between two CUDA "
+                      "events on the launching stream; every entry streams more than the 126 MB L2 per launch except "
+                      "mass P=1 fp32 (96 MB)"}
     if world == 1 and not a.no_cpu_baseline:
         threads = os.cpu_count() or 1
+        triple, tuning = cpu_tuning(a)
         sample_cells = min(cells, 262144)
-        res = cpu_reference_rate(a, sample_cells, threads, reps=20, want_output=4096)
+        res = cpu_reference_rate(a, sample_cells, threads, reps=20, want_output=4096, triple=triple)
         W_cpu = res["head"]
         W_main_head = W_main_head[:W_cpu.size]
         line["cpu_baseline"] = {"value": res["rate"], "unit": "GDoF/s", "cores": threads, "kind": res["kind"],
-                                "sample": res["desc"]}
+                                "sample": res["desc"], "cpu": cpu_model(), "tuning": tuning}
+        # the reference's own problem size (run.sh:9: Ndofs = 1e6, cache resident) per worker, all cores, same knobs
+        small = cpu_reference_rate(a, threads * max(1, 1_000_000 // nd), threads, reps=20, triple=triple)
+        line["cpu_baseline"]["cache_resident"] = {"value": small["rate"], "unit": "GDoF/s", "cores": threads,
+                                                  "sample": small["desc"]}
         if a.mode == "ref_exact" or a.op == "mass":
             # the CPU baseline ran the same cells of the same synthetic inputs: compare its output
             err = float(np.abs(W_main_head.astype(np.float64) - W_cpu.astype(np.float64)).max()

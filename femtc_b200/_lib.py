@@ -42,6 +42,7 @@ def _load() -> C.CDLL:
         getattr(lib, f"femtc_checksum_device_{s}").argtypes = [vp, sz, vp, vp]
         getattr(lib, f"femtc_fill_uniform_device_{s}").argtypes = [vp, sz, u64, u64, u64, i, vp]
         getattr(lib, f"femtc_operator_create_{s}").argtypes = [C.POINTER(vp), i, vp, sz, vp, sz, i, i]
+    lib.femtc_stream_probe_device.argtypes = [vp, vp, sz, i, vp]
     lib.femtc_operator_apply.argtypes = [vp, vp, vp]
     lib.femtc_operator_apply_device.argtypes = [vp, vp, vp, vp]
     lib.femtc_operator_device_bytes.argtypes = [vp]
@@ -87,5 +88,5 @@ def get_option(name: str) -> int:
 def kernel_info(op: str, dtype_bytes: int, degree: int, mode: int = 0) -> dict:
     info = (C.c_longlong * 8)()
     check(lib.femtc_kernel_info(0 if op == "mass" else 1, dtype_bytes, degree, mode, info))
-    keys = ("family", "cells_per_tile", "threads", "smem_bytes", "blocks_per_sm", "regs", "grid", "reserved")
+    keys = ("family", "cells_per_tile", "threads", "smem_bytes", "blocks_per_sm", "regs", "grid", "detail")
     return dict(zip(keys, [int(v) for v in info]))

@@ -478,10 +478,7 @@ long long run_mass_cell(const MassArgs<T>& a)
     return -rc;
   const long long blocks_needed = (rounds + p.warps_per_block - 1) / p.warps_per_block;
   const int grid = (int)std::min<long long>(blocks_needed, (long long)sm_count() * p.blocks_per_sm);
-  kernel<<<grid, p.warps_per_block * 32, p.smem, a.stream>>>(B, a.U, a.W, a.detJ, rounds);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_CELL, NS, 32, p.blocks_per_sm, kernel, grid, p.warps_per_block * 32, p.smem, a.stream, B, a.U, a.W, a.detJ, rounds);
   return rounds * 32;
 }
 
@@ -505,10 +502,7 @@ long long run_stiff_cell(const StiffnessArgs<T>& a)
     return -rc;
   const long long blocks_needed = (rounds + p.warps_per_block - 1) / p.warps_per_block;
   const int grid = (int)std::min<long long>(blocks_needed, (long long)sm_count() * p.blocks_per_sm);
-  kernel<<<grid, p.warps_per_block * 32, p.smem, a.stream>>>(B, a.U, a.W, a.G, rounds);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_CELL, NS, 32, p.blocks_per_sm, kernel, grid, p.warps_per_block * 32, p.smem, a.stream, B, a.U, a.W, a.G, rounds);
   return rounds * 32;
 }
 

@@ -1543,10 +1543,7 @@ long long run_mass_col(const MassArgs<T>& a)
   if (rc)
     return -rc;
   const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
-  kernel<<<grid, G::NT, MC::smem_bytes, a.stream>>>(B, a.U, a.W, a.detJ, ntiles);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_COLUMN, 1, C, bps, kernel, grid, G::NT, MC::smem_bytes, a.stream, B, a.U, a.W, a.detJ, ntiles);
   return ntiles * C;
 }
 
@@ -1567,10 +1564,7 @@ long long run_mass_col2(const MassArgs<T>& a)
   if (rc)
     return -rc;
   const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
-  kernel<<<grid, H::NT, MC::smem_bytes, a.stream>>>(B, a.U, a.W, a.detJ, ntiles);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_COLUMN, 2, C, bps, kernel, grid, H::NT, MC::smem_bytes, a.stream, B, a.U, a.W, a.detJ, ntiles);
   return ntiles * C;
 }
 
@@ -1593,10 +1587,7 @@ long long run_stiff_col(const StiffnessArgs<T>& a)
   if (rc)
     return -rc;
   const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
-  kernel<<<grid, SC::threads, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_COLUMN, 1 + 10 * NG + (PW ? 1000 : 0), C, bps, kernel, grid, SC::threads, SC::smem_bytes, a.stream, B, a.U, a.W, a.G, ntiles);
   return ntiles * C;
 }
 
@@ -1618,10 +1609,7 @@ long long run_stiff_col2(const StiffnessArgs<T>& a)
   if (rc)
     return -rc;
   const int grid = (int)std::min<long long>(ntiles, (long long)sm_count() * bps);
-  kernel<<<grid, SC::threads, SC::smem_bytes, a.stream>>>(B, a.U, a.W, a.G, ntiles);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_COLUMN, 2 + 10 * NG + 1000, C, bps, kernel, grid, SC::threads, SC::smem_bytes, a.stream, B, a.U, a.W, a.G, ntiles);
   return ntiles * C;
 }
 // two cells per thread: tile sizes per shape (fp32 tiles must be whole 16-byte units)

@@ -26,6 +26,54 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 void count_launch(int n = 1);
 
+// ---- launch record (femtc_kernel_info) -------------------------------------------------------------
+// Every operator launcher goes through FEMTC_LAUNCH: it notes what is about to run in a thread-local record and,
+// unless the calling thread is in a dry run (femtc_kernel_info walks the dispatcher that way), launches it.
+enum KernelFamily
+{
+  FAMILY_GENERIC = 0,
+  FAMILY_SLAB = 1,   // tiled_kernels.cu
+  FAMILY_CELL = 2,   // cell_kernels.cu
+  FAMILY_COLUMN = 3, // column_kernels.cu
+  FAMILY_TC = 4      // tc_kernels.cu (DMMA) / tf32_kernels.cu
+};
+struct LaunchRecord
+{
+  int family = 0, cells_per_tile = 0, threads = 0, blocks_per_sm = 0, regs = 0, detail = 0;
+  long long smem = 0, grid = 0;
+};
+bool dry_run();
+LaunchRecord& launch_record();
+template <typename K>
+inline void note_launch(int family, int detail, K kernel, int cells_per_tile, int blocks_per_sm, long long grid,
+                        int threads, size_t smem)
+{
+  LaunchRecord& r = launch_record();
+  r.family = family, r.detail = detail, r.cells_per_tile = cells_per_tile, r.blocks_per_sm = blocks_per_sm;
+  r.grid = grid, r.threads = threads, r.smem = (long long)smem, r.regs = 0;
+  if (dry_run())
+  {
+    cudaFuncAttributes fa{};
+    if (cudaFuncGetAttributes(&fa, kernel) == cudaSuccess)
+      r.regs = fa.numRegs;
+    else
+      (void)cudaGetLastError();
+  }
+}
+// `detail`: family-specific variant code for reports (cells per thread, ring depth, ...)
+#define FEMTC_LAUNCH(family, detail, cells_per_tile, bps, kernel, grid, threads, smem, stream, ...)             \
+  do                                                                                                            \
+  {                                                                                                             \
+    ::femtc::note_launch(family, detail, kernel, cells_per_tile, bps, grid, threads, smem);                     \
+    if (!::femtc::dry_run())                                                                                    \
+    {                                                                                                           \
+      kernel<<<grid, threads, smem, stream>>>(__VA_ARGS__);                                                     \
+      ::femtc::count_launch();                                                                                  \
+      if (cudaGetLastError() != cudaSuccess)                                                                    \
+        return -FEMTC_ERR_CUDA;                                                                                 \
+    }                                                                                                           \
+  } while (0)
+
 // ---- problem description handed to the launchers ----------------------------------------
 template <typename T>
 struct MassArgs
@@ -72,6 +120,8 @@ template <typename T>
 int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
                         int centred, cudaStream_t s);
 
+int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, int reads, cudaStream_t s);
+
 // tiled_kernels.cu -- degrees 1..8, TMA-staged warp tiles.  Return value:
 //   >= 0 : number of leading cells processed on the fast path (the caller runs the generic
 //          kernel on the remainder); < 0 : -(FEMTC_ERR_*).
@@ -95,7 +145,6 @@ template <typename T>
 long long launch_mass_tc(const MassArgs<T>& a);
 template <typename T>
 long long launch_stiffness_tc(const StiffnessArgs<T>& a);
-int tiled_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8]);
 
 int sm_count();
 

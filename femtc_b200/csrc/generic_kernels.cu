@@ -10,6 +10,10 @@
 // so three sweeps walk the three axes and come back to the natural index order.
 #include "common.cuh"
 
+#include <mutex>
+#include <set>
+#include <utility>
+
 namespace femtc
 {
 namespace
@@ -327,13 +331,46 @@ fill_uniform_kernel(T* x, size_t n, uint64_t base, int centred)
 // shared-memory budget we are willing to request for the generic kernels
 constexpr size_t kGenericSmemMax = 160 * 1024;
 
+// The opt-in ceiling is a property of (kernel, device): it is raised ONCE to the largest size any degree asks for,
+// so two host threads launching different degrees never interleave an attribute change with a launch.
 template <typename K>
-int opt_in_smem(K kernel, size_t bytes)
+int opt_in_smem(K kernel)
 {
-  if (bytes > 48 * 1024)
-    FEMTC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  int dev = 0;
+  FEMTC_CUDA(cudaGetDevice(&dev));
+  const auto key = std::make_pair(reinterpret_cast<const void*>(kernel), dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (done.count(key))
+    return FEMTC_OK;
+  FEMTC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGenericSmemMax));
+  done.insert(key);
   return FEMTC_OK;
 }
+
+// stream-ordered scratch that is handed back on every exit path
+struct AsyncBuf
+{
+  void* p = nullptr;
+  cudaStream_t s = nullptr;
+  AsyncBuf() = default;
+  AsyncBuf(const AsyncBuf&) = delete;
+  AsyncBuf& operator=(const AsyncBuf&) = delete;
+  ~AsyncBuf()
+  {
+    if (p && cudaFreeAsync(p, s) != cudaSuccess)
+      (void)cudaGetLastError();
+  }
+  int alloc(size_t bytes, cudaStream_t stream)
+  {
+    s = stream;
+    FEMTC_CUDA(cudaMallocAsync(&p, bytes, stream));
+    return FEMTC_OK;
+  }
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
 
 } // namespace
 
@@ -346,31 +383,33 @@ int launch_mass_generic(const MassArgs<T>& a)
     return FEMTC_OK;
   const int n1 = a.degree + 1, n2 = n1 * n1;
   const size_t nd = (size_t)n2 * n1;
-  T* dphi = nullptr;
-  FEMTC_CUDA(cudaMallocAsync(&dphi, n2 * sizeof(T), a.stream));
-  FEMTC_CUDA(cudaMemcpyAsync(dphi, a.phi_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
-
   int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
   size_t smem = (n2 + 2 * cpb * nd) * sizeof(T);
-  T* ws = nullptr;
   const size_t groups = (a.num_cells + cpb - 1) / cpb;
   int grid = (int)min(groups, (size_t)sm_count() * 8);
-  if (smem > kGenericSmemMax)
+  const bool spill = smem > kGenericSmemMax; // the per-cell work arrays live in global scratch instead
+  if (spill)
   {
     cpb = 1;
     smem = n2 * sizeof(T);
     grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
-    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * 2 * nd * sizeof(T), a.stream));
   }
-  int rc = opt_in_smem(mass_generic_kernel<T>, smem);
+  note_launch(FAMILY_GENERIC, spill, mass_generic_kernel<T>, cpb, 0, grid, kThreads, smem);
+  if (dry_run())
+    return FEMTC_OK;
+  AsyncBuf dphi, ws;
+  int rc = dphi.alloc(n2 * sizeof(T), a.stream);
   if (rc)
     return rc;
-  mass_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi, a.U, a.W, a.detJ, a.num_cells, n1, cpb, ws);
+  FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.phi_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  if (spill && (rc = ws.alloc((size_t)grid * 2 * nd * sizeof(T), a.stream)))
+    return rc;
+  if ((rc = opt_in_smem(mass_generic_kernel<T>)))
+    return rc;
+  mass_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), a.U, a.W, a.detJ, a.num_cells, n1, cpb,
+                                                             ws.as<T>());
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
-  if (ws)
-    FEMTC_CUDA(cudaFreeAsync(ws, a.stream));
-  FEMTC_CUDA(cudaFreeAsync(dphi, a.stream));
   return FEMTC_OK;
 }
 
@@ -381,33 +420,34 @@ int launch_stiffness_generic(const StiffnessArgs<T>& a)
     return FEMTC_OK;
   const int n1 = a.degree + 1, n2 = n1 * n1;
   const size_t nd = (size_t)n2 * n1;
-  T* dphi = nullptr;
-  FEMTC_CUDA(cudaMallocAsync(&dphi, 2 * n2 * sizeof(T), a.stream));
-  FEMTC_CUDA(cudaMemcpyAsync(dphi, a.A_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
-  FEMTC_CUDA(cudaMemcpyAsync(dphi + n2, a.D_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
-
   int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
   size_t smem = (2 * n2 + 5 * cpb * nd) * sizeof(T);
-  T* ws = nullptr;
   const size_t groups = (a.num_cells + cpb - 1) / cpb;
   int grid = (int)min(groups, (size_t)sm_count() * 8);
-  if (smem > kGenericSmemMax)
+  const bool spill = smem > kGenericSmemMax;
+  if (spill)
   {
     cpb = 1;
     smem = 2 * n2 * sizeof(T);
     grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
-    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * 5 * nd * sizeof(T), a.stream));
   }
-  int rc = opt_in_smem(stiffness_generic_kernel<T>, smem);
+  note_launch(FAMILY_GENERIC, spill, stiffness_generic_kernel<T>, cpb, 0, grid, kThreads, smem);
+  if (dry_run())
+    return FEMTC_OK;
+  AsyncBuf dphi, ws;
+  int rc = dphi.alloc(2 * n2 * sizeof(T), a.stream);
   if (rc)
     return rc;
-  stiffness_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi, dphi + n2, a.U, a.W, a.G, a.num_cells,
-                                                                n1, cpb, a.mode, ws);
+  FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.A_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  FEMTC_CUDA(cudaMemcpyAsync(dphi.as<T>() + n2, a.D_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  if (spill && (rc = ws.alloc((size_t)grid * 5 * nd * sizeof(T), a.stream)))
+    return rc;
+  if ((rc = opt_in_smem(stiffness_generic_kernel<T>)))
+    return rc;
+  stiffness_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), dphi.as<T>() + n2, a.U, a.W, a.G,
+                                                                  a.num_cells, n1, cpb, a.mode, ws.as<T>());
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
-  if (ws)
-    FEMTC_CUDA(cudaFreeAsync(ws, a.stream));
-  FEMTC_CUDA(cudaFreeAsync(dphi, a.stream));
   return FEMTC_OK;
 }
 
@@ -443,20 +483,19 @@ int launch_apply_contractions(int Na, int Nb, int Tr, const T* dI0, const T* dI1
   const size_t na = Na, nb = Nb;
   size_t smem = (na * nb * nb + na * na * nb) * sizeof(T);
   int grid = (int)min(batch, (size_t)sm_count() * 8);
-  T* ws = nullptr;
+  AsyncBuf ws;
+  int rc = FEMTC_OK;
   if (smem > kGenericSmemMax)
   {
-    FEMTC_CUDA(cudaMallocAsync(&ws, (size_t)grid * smem, s));
+    if ((rc = ws.alloc((size_t)grid * smem, s)))
+      return rc;
     smem = 0;
   }
-  int rc = opt_in_smem(apply_contractions_kernel<T>, smem);
-  if (rc)
+  if ((rc = opt_in_smem(apply_contractions_kernel<T>)))
     return rc;
-  apply_contractions_kernel<T><<<grid, kThreads, smem, s>>>(Na, Nb, Tr, dI0, dI1, dI2, dB, dA, batch, ws);
+  apply_contractions_kernel<T><<<grid, kThreads, smem, s>>>(Na, Nb, Tr, dI0, dI1, dI2, dB, dA, batch, ws.as<T>());
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
-  if (ws)
-    FEMTC_CUDA(cudaFreeAsync(ws, s));
   return FEMTC_OK;
 }
 
@@ -483,6 +522,49 @@ int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint
   const uint64_t base = seed + stream_id * 0x9E3779B97F4A7C15ull + offset;
   const int grid = (int)min((n + 255) / 256, (size_t)sm_count() * 16);
   fill_uniform_kernel<T><<<grid, 256, 0, s>>>(dX, n, base, centred);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+// ---- streaming probe: the operators' traffic mix without their arithmetic --------------------------------
+// out[i] = in_0[i] + ... + in_{R-1}[i] over 16-byte words, streams back to back in `in`.  R reads : 1 write per word is
+// the mix of the stiffness (7:1) and mass (2:1) action; a device copy is 1:1.  bench.py times it as the roofline
+// denominator for a read-dominated stream next to the copy bandwidth of MEASURED_PEAKS.json.
+template <int R>
+__global__ void __launch_bounds__(256) stream_probe_kernel(const float4* __restrict__ in, float4* __restrict__ out,
+                                                           size_t n)
+{
+  const size_t stride = (size_t)gridDim.x * 256;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride)
+  {
+    float4 v[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      v[r] = __ldcs(in + (size_t)r * n + i);
+    float4 acc = v[0];
+#pragma unroll
+    for (int r = 1; r < R; ++r)
+      acc.x += v[r].x, acc.y += v[r].y, acc.z += v[r].z, acc.w += v[r].w;
+    __stcs(out + i, acc);
+  }
+}
+
+int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, int reads, cudaStream_t s)
+{
+  const size_t n = bytes_per_stream / 16;
+  if (n == 0)
+    return FEMTC_OK;
+  const int grid = (int)min((n + 255) / 256, (size_t)sm_count() * 8);
+  const float4* in = static_cast<const float4*>(d_in);
+  float4* out = static_cast<float4*>(d_out);
+  switch (reads)
+  {
+  case 1: stream_probe_kernel<1><<<grid, 256, 0, s>>>(in, out, n); break;
+  case 2: stream_probe_kernel<2><<<grid, 256, 0, s>>>(in, out, n); break;
+  case 7: stream_probe_kernel<7><<<grid, 256, 0, s>>>(in, out, n); break;
+  default: set_error("stream probe: reads must be 1, 2 or 7"); return FEMTC_ERR_ARG;
+  }
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
   return FEMTC_OK;

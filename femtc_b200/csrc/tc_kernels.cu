@@ -38,6 +38,9 @@
 // Semantics follow the reference as coded (REF_EXACT: include/femtc_b200.h).  FULL stays on the
 // column kernels.
 #include "common.cuh"
+
+#include <map>
+#include <mutex>
 #include "tma.cuh"
 
 #include <algorithm>
@@ -560,27 +563,38 @@ long long run_tc(const double* A, const double* D, const double* U, double* W, c
     B.d[i] = D[i];
   }
   auto kernel = tc_kernel<N1, OP, NGS, NW>;
-  int dev = 0, max_optin = 0, bps = 0;
+  // the plan of a kernel on a device never changes: attributes and the occupancy query are paid on the first launch only
+  static std::mutex mu;
+  static std::map<int, int> plans; // device -> resident blocks per SM
+  int dev = 0, bps = 0;
   FEMTC_CUDA(cudaGetDevice(&dev));
-  FEMTC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  if (max_optin < PL::smem_bytes)
   {
-    set_error("tensor-core kernel does not fit on an SM");
-    return -FEMTC_ERR_CUDA;
-  }
-  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PL::smem_bytes) != cudaSuccess ||
-      cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) != cudaSuccess ||
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32 * NW, PL::smem_bytes) != cudaSuccess || bps < 1)
-  {
-    (void)cudaGetLastError();
-    set_error("tensor-core kernel: launch planning failed");
-    return -FEMTC_ERR_CUDA;
+    std::lock_guard<std::mutex> lock(mu);
+    const auto it = plans.find(dev);
+    if (it != plans.end())
+      bps = it->second;
+    else
+    {
+      int max_optin = 0;
+      FEMTC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+      if (max_optin < PL::smem_bytes)
+      {
+        set_error("tensor-core kernel does not fit on an SM");
+        return -FEMTC_ERR_CUDA;
+      }
+      if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PL::smem_bytes) != cudaSuccess ||
+          cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100) != cudaSuccess ||
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, 32 * NW, PL::smem_bytes) != cudaSuccess || bps < 1)
+      {
+        (void)cudaGetLastError();
+        set_error("tensor-core kernel: launch planning failed");
+        return -FEMTC_ERR_CUDA;
+      }
+      plans[dev] = bps;
+    }
   }
   const int grid = (int)std::min<long long>(ncells, (long long)sm_count() * bps);
-  kernel<<<grid, 32 * NW, PL::smem_bytes, stream>>>(B, U, W, geom, ncells);
-  count_launch();
-  if (cudaGetLastError() != cudaSuccess)
-    return -FEMTC_ERR_CUDA;
+  FEMTC_LAUNCH(FAMILY_TC, NW + 10 * NGS, 1, bps, kernel, grid, 32 * NW, PL::smem_bytes, stream, B, U, W, geom, ncells);
   return ncells;
 }
 

@@ -194,6 +194,12 @@ int femtc_fill_uniform_device_f64(double* dX, size_t n, uint64_t seed, uint64_t 
 int femtc_fill_uniform_device_f32(float* dX, size_t n, uint64_t seed, uint64_t stream_id,
                                   uint64_t offset, int centred, void* stream);
 
+/* Streaming probe for the roofline denominator: d_out[i] = d_in[i] + d_in[n+i] + ... over `reads` back-to-back
+ * streams of bytes_per_stream bytes each (16-byte words, fp32 adds).  reads = 7 / 2 is the read:write mix of the
+ * stiffness / mass action (bench_stiffness.cpp:123-124 counts the same streams), 1 is a device copy.  No
+ * reference counterpart; measurement only. */
+int femtc_stream_probe_device(const void* d_in, void* d_out, size_t bytes_per_stream, int reads, void* stream);
+
 /* ---- runtime --------------------------------------------------------------------------- */
 int femtc_device_count(void);             /* number of usable sm_100 devices, 0 if none */
 int femtc_set_device(int device);         /* device used by the calling thread */
@@ -212,6 +218,11 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
  *                     calls on the same buffers (bench_mass.cpp:95-105) DMA at the PCIe rate.  The
  *                     caller must call femtc_release_cache() before freeing such a buffer.  Default 0,
  *                     or 1 when FEMTC_HOST_REGISTER=1 is in the environment at load time.
+ *   "host_devices"    n > 1: ONE host-pointer operator call is cut into n contiguous cell ranges served by devices
+ *                     0..n-1 concurrently (one worker thread and one three-slot copy/compute pipeline per device), so
+ *                     the unchanged drivers (bench_stiffness.cpp:95-105) move their fields over n PCIe links.  The
+ *                     action is cell-local: the result is bit-identical to the one-device call.  Default 1, or
+ *                     FEMTC_HOST_DEVICES from the environment at load time; clamped to the visible devices.
  *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
  *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
  *   "variant"         development knob for A/B measurements (0 = tuned defaults).  1, 2: alternative pipeline
@@ -224,10 +235,13 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
 int femtc_set_option(const char* name, long long value);
 long long femtc_get_option(const char* name);
 
-/* Which kernel serves (op, dtype, degree, mode) on the fast path, for reports:
+/* Which kernel serves a large aligned batch of (op, dtype, degree, mode) on the calling thread's device, under the
+ * current options -- for reports.  The real dispatcher is walked in a dry run (nothing is launched).
  * op 0 = mass, 1 = stiffness; dtype_bytes 4 or 8.  Fills info[0..7] =
- * {kernel family (0 generic, 1 tiled), cells per tile, threads per block, dynamic smem bytes,
- *  blocks per SM, registers per thread, grid blocks, reserved}. */
+ * {kernel family (0 generic, 1 slab, 2 one-thread-per-cell, 3 column, 4 tensor core), cells per tile (slab: per warp round),
+ *  threads per block, dynamic smem bytes, resident blocks per SM (0: not planned), registers per thread, grid blocks,
+ *  family-specific detail (column: cells per thread + 10 x ring depth + 1000 if block-wide ring; tensor core: warps
+ *  per cell + 10 x ring slots; slab: geometry ring depth; cell: pipeline stages)}. */
 int femtc_kernel_info(int op, int dtype_bytes, int degree, int mode, long long info[8]);
 
 #ifdef __cplusplus

@@ -173,6 +173,93 @@ def test_host_register_option_pins_caller_buffers_once(femtc, oracle):
     assert np.array_equal(W0, run_host(femtc, "stiffness", phi, U, geom, P))
 
 
+def test_host_register_grows_with_a_larger_buffer_at_the_same_address(femtc, oracle):
+    """A registration that only partly covers a later, larger call at the same base (the caller freed and
+    reallocated, or passed a longer prefix of one array) is replaced by one that covers the whole range."""
+    import torch
+    P, nc = 3, 60000
+    phi, U, geom = splitmix(oracle, "stiffness", P, nc, "float64", seed=78, centred=True)
+    femtc.set_option("host_register", 1)
+    try:
+        half = nc // 2
+        nd = (P + 1) ** 3
+        W_half = run_host(femtc, "stiffness", phi, U[:half * nd], geom[:half * nd * 6], P)
+        W_all = run_host(femtc, "stiffness", phi, U, geom, P)
+        assert np.array_equal(W_all[:half * nd], W_half)
+        assert torch.from_numpy(geom[-1024:]).is_pinned() and torch.from_numpy(U[-1024:]).is_pinned()
+        assert rel_err(W_all, oracle_run(oracle, "stiffness", phi, U, geom, P)) <= TOL["float64"]
+    finally:
+        femtc.set_option("host_register", 0)
+        femtc._lib.lib.femtc_release_cache()
+    assert not torch.from_numpy(geom).is_pinned()
+
+
+@pytest.mark.parametrize("op,mode,P,dt", [("stiffness", 0, 3, "float64"), ("mass", 0, 4, "float32"), ("stiffness", 1, 6, "float64")])
+def test_one_host_call_fanned_out_over_all_devices(femtc, oracle, op, mode, P, dt):
+    """Option "host_devices" = n: one host-pointer call is cut into n contiguous cell ranges, one per device; the
+    action is cell-local, so the result is bit-identical to the one-device call (bench_stiffness.cpp:95-105 unchanged
+    then uses n PCIe links)."""
+    ndev = femtc.device_count()
+    if ndev < 2:
+        pytest.skip("needs at least two visible B200s")
+    nc = 16 * 96 * ndev * 3 + 16 * 7   # shares of whole tiles (any family) + a tail on the last device
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=5)
+    one = run_host(femtc, op, phi, U, geom, P, mode)
+    launches0 = femtc.get_option("launches")
+    femtc.set_option("host_devices", ndev)
+    femtc.set_option("host_chunk_mb", 1)
+    try:
+        many = run_host(femtc, op, phi, U, geom, P, mode)
+        assert femtc.get_option("host_devices") == ndev
+    finally:
+        femtc.set_option("host_devices", 1)
+        femtc.set_option("host_chunk_mb", 64)
+    assert femtc.get_option("launches") - launches0 >= ndev
+    assert np.array_equal(one, many)
+    assert elementwise_rel_err(many, oracle_run(oracle, op, phi, U, geom, P, mode)) <= TOL[dt]
+
+
+def test_kernel_info_reports_the_family_that_serves_each_shape(femtc):
+    """femtc_kernel_info walks the real dispatcher in a dry run: nothing is launched, the record names the family."""
+    launches0 = femtc.get_option("launches")
+    seen = set()
+    for op in ("mass", "stiffness"):
+        for size in (8, 4):
+            for P in range(1, 11):
+                for mode in ((0,) if op == "mass" else (0, 1)):
+                    info = femtc.kernel_info(op, size, P, mode)
+                    seen.add(info["family"])
+                    assert info["threads"] > 0 and info["grid"] > 0
+                    if P <= 8:
+                        assert info["family"] in (1, 2, 3, 4), (op, size, P, mode, info)
+                        assert info["regs"] > 0 and info["blocks_per_sm"] >= 1 and info["cells_per_tile"] >= 1
+                    else:
+                        assert info["family"] == 0
+    assert seen == {0, 1, 2, 3, 4}
+    assert femtc.get_option("launches") == launches0
+    assert femtc.kernel_info("stiffness", 8, 3, 0)["family"] == 1          # the headline runs on the slab kernel
+    femtc.set_option("kernel", 1)
+    try:
+        assert femtc.kernel_info("stiffness", 8, 3, 0)["family"] == 0
+    finally:
+        femtc.set_option("kernel", 0)
+
+
+def test_stream_probe_sums_its_streams(femtc, torch_cuda):
+    torch = torch_cuda
+    n = 1 << 20
+    src = torch.rand(7 * n, dtype=torch.float32, device="cuda")
+    for reads in (1, 2, 7):
+        dst = torch.zeros(n, dtype=torch.float32, device="cuda")
+        femtc._lib.check(femtc._lib.lib.femtc_stream_probe_device(src.data_ptr(), dst.data_ptr(), 4 * n, reads,
+                                                                 torch.cuda.current_stream().cuda_stream))
+        ref = src[:n].clone()
+        for r in range(1, reads):
+            ref += src[r * n:(r + 1) * n]
+        assert torch.equal(dst, ref)
+    assert femtc._lib.lib.femtc_stream_probe_device(src.data_ptr(), dst.data_ptr(), 4 * n, 3, 0) != 0
+
+
 @pytest.mark.parametrize("op,mode", CASES)
 def test_generic_and_tiled_kernels_agree(femtc, oracle, torch_cuda, op, mode):
     P, dt, nc = 3, "float64", 2048
