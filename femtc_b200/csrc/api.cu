@@ -344,6 +344,7 @@ static void maybe_register(const void* ptr, size_t bytes)
   if (!g_opt_host_register.load() || !ptr || bytes < (size_t(1) << 20))
     return;
   const uintptr_t base = reinterpret_cast<uintptr_t>(ptr), end = base + bytes;
+  static const bool debug = env_flag("FEMTC_DEBUG_REGISTER"); // development: log every decision on stderr
   std::lock_guard<std::mutex> lock(g_reg_mu);
   // One of our own registrations that covers the range: done.  One that only overlaps it is stale (the caller
   // freed the buffer and got the address again with another size) or too short: drop it and register afresh.
@@ -351,9 +352,15 @@ static void maybe_register(const void* ptr, size_t bytes)
   {
     const uintptr_t b = it->first, e = b + it->second;
     if (b <= base && end <= e)
+    {
+      if (debug)
+        std::fprintf(stderr, "femtc_b200: %p +%zu covered by an earlier registration\n", ptr, bytes);
       return;
+    }
     if (b < end && base < e)
     {
+      if (debug)
+        std::fprintf(stderr, "femtc_b200: %p +%zu overlaps own entry %p +%zu: dropping it\n", ptr, bytes, (void*)b, it->second);
       if (cudaHostUnregister(reinterpret_cast<void*>(b)) != cudaSuccess)
         (void)cudaGetLastError();
       it = g_registered.erase(it);
@@ -365,8 +372,15 @@ static void maybe_register(const void* ptr, size_t bytes)
   // range has to be, first byte to last; a partly covered range cannot be completed in place and stays as it is
   const bool first = page_locked(ptr), last = page_locked(reinterpret_cast<const char*>(ptr) + bytes - 1);
   if (first || last)
+  {
+    if (debug)
+      std::fprintf(stderr, "femtc_b200: register %p +%zu: already page-locked (first %d, last %d)\n", ptr, bytes, first, last);
     return;
-  if (cudaHostRegister(const_cast<void*>(ptr), bytes, cudaHostRegisterPortable) == cudaSuccess)
+  }
+  const cudaError_t e = cudaHostRegister(const_cast<void*>(ptr), bytes, cudaHostRegisterPortable);
+  if (debug)
+    std::fprintf(stderr, "femtc_b200: register %p +%zu: %s\n", ptr, bytes, cudaGetErrorString(e));
+  if (e == cudaSuccess)
     g_registered[base] = bytes;
   else
     (void)cudaGetLastError(); // overlaps a foreign registration, or not registrable: stay on the pageable path
@@ -379,6 +393,22 @@ static void unregister_all()
     if (cudaHostUnregister(reinterpret_cast<void*>(r.first)) != cudaSuccess)
       (void)cudaGetLastError();
   g_registered.clear();
+}
+
+// Chunk and share boundaries of the host-pointer path fall on multiples of cut_cells(n1) cells: 16-byte aligned in every
+// array for any dtype (TMA path), and a whole number of tiles of every kernel family that serves that n1 (slab rounds
+// of 32/n1 cells and pairs of them, 32-cell rounds of the one-thread-per-cell kernels, column tiles), so each cell is
+// served by the same kernel as in an unchunked call and the result depends neither on the chunk size nor on the fan-out.
+static size_t cut_cells(size_t nd)
+{
+  switch (nd)
+  {
+  case 8: return 64;     // n1 = 2: rounds of 16 / 32, column tile 64
+  case 27: return 1120;  // n1 = 3: rounds of 10 / 32, column tile 28
+  case 125: return 240;  // n1 = 5: pairs of 6-cell rounds, column tiles 8 / 10
+  case 216: return 560;  // n1 = 6: rounds of 5, column tiles 7 / 8 / 14 / 16
+  default: return 16;    // n1 = 4, 7, 8, 9: tiles of 2 / 4 / 8; generic kernel: any
+  }
 }
 
 // One device's share of a host-pointer call: the calling thread's current device sweeps `num_cells` cells in chunks.
@@ -401,8 +431,9 @@ static int host_pipeline_device(const T* U, T* W, const T* geom, int geom_width,
   }
   const size_t bytes_per_cell = nd * sizeof(T) * (1 + (geom_dev ? 0 : geom_width));
   size_t chunk_cells = std::max<size_t>(1, ((size_t)g_opt_host_chunk_mb.load() << 20) / bytes_per_cell);
-  // keep chunk boundaries 16-byte aligned in every array so the TMA path applies to all chunks
-  chunk_cells = std::max<size_t>(16, chunk_cells & ~size_t(15));
+  // chunk boundaries on whole tiles of every kernel family (cut_cells above)
+  const size_t kCutCells = cut_cells(nd);
+  chunk_cells = std::max<size_t>(kCutCells, chunk_cells / kCutCells * kCutCells);
   chunk_cells = std::min(chunk_cells, std::max<size_t>(num_cells, 1));
 
   int rc = FEMTC_OK;
@@ -455,8 +486,9 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
   maybe_register(W, num_cells * nd * sizeof(T));
   if (!geom_dev)
     maybe_register(geom, num_cells * nd * geom_width * sizeof(T));
+  const size_t kCutCells = cut_cells(nd);
   int ndev = (int)std::min<long long>(g_opt_host_devices.load(), g_usable_devices);
-  if (geom_dev || ndev < 2 || num_cells < (size_t)ndev * 64)
+  if (geom_dev || ndev < 2 || num_cells < (size_t)ndev * kCutCells)
     return host_pipeline_device<T>(U, W, geom, geom_width, num_cells, nd, launch, geom_dev);
 
   int home = 0;
@@ -464,7 +496,7 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
   std::vector<int> rcs(ndev, FEMTC_OK);
   std::vector<std::string> errs(ndev);
   std::vector<std::thread> workers;
-  auto cut = [&](int r) { return r == ndev ? num_cells : (num_cells * r / ndev) & ~size_t(15); };
+  auto cut = [&](int r) { return r == ndev ? num_cells : (num_cells * r / ndev) / kCutCells * kCutCells; };
   for (int r = 0; r < ndev; ++r)
   {
     const size_t c0 = cut(r), c1 = cut(r + 1);

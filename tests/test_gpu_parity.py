@@ -153,6 +153,7 @@ def test_host_register_option_pins_caller_buffers_once(femtc, oracle):
     """Option "host_register": pageable caller buffers are page-locked in place on first sight and the
     registration is reused; results are unchanged; femtc_release_cache() drops the registrations."""
     import torch
+    torch.cuda.init()                                       # Tensor.is_pinned() answers False before torch's own CUDA init
     P, nc = 3, 40000                                        # 20 MB fields, 120 MB geometry
     phi, U, geom = splitmix(oracle, "stiffness", P, nc, "float64", seed=77, centred=True)
     W0 = run_host(femtc, "stiffness", phi, U, geom, P)
@@ -177,6 +178,7 @@ def test_host_register_grows_with_a_larger_buffer_at_the_same_address(femtc, ora
     """A registration that only partly covers a later, larger call at the same base (the caller freed and
     reallocated, or passed a longer prefix of one array) is replaced by one that covers the whole range."""
     import torch
+    torch.cuda.init()
     P, nc = 3, 60000
     phi, U, geom = splitmix(oracle, "stiffness", P, nc, "float64", seed=78, centred=True)
     femtc.set_option("host_register", 1)
@@ -217,6 +219,27 @@ def test_one_host_call_fanned_out_over_all_devices(femtc, oracle, op, mode, P, d
     assert femtc.get_option("launches") - launches0 >= ndev
     assert np.array_equal(one, many)
     assert elementwise_rel_err(many, oracle_run(oracle, op, phi, U, geom, P, mode)) <= TOL[dt]
+
+
+@pytest.mark.parametrize("dt", DTYPES)
+@pytest.mark.parametrize("P", range(1, 9))
+@pytest.mark.parametrize("op,mode", CASES)
+def test_host_chunking_does_not_change_a_bit(femtc, oracle, torch_cuda, op, mode, P, dt):
+    """The host-pointer path cuts its chunks on whole tiles of every kernel family, so a call swept in many small chunks
+    equals the one-launch device-pointer call bit for bit (and stays within tolerance of the oracle)."""
+    nd = (P + 1) ** 3
+    size = 8 if dt == "float64" else 4
+    per_cell = nd * size * (2 + (6 if op == "stiffness" else 1))
+    nc = max(3500, min(40000, (5 << 20) // per_cell)) + 37          # several 1 MB chunks and a ragged end
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=12)
+    dev = run_device(femtc, torch_cuda, op, phi, U, geom, P, mode)
+    femtc.set_option("host_chunk_mb", 1)
+    try:
+        host = run_host(femtc, op, phi, U, geom, P, mode)
+    finally:
+        femtc.set_option("host_chunk_mb", 64)
+    assert np.array_equal(host, dev)
+    assert elementwise_rel_err(host, oracle_run(oracle, op, phi, U, geom, P, mode)) <= TOL[dt]
 
 
 def test_kernel_info_reports_the_family_that_serves_each_shape(femtc):
