@@ -19,7 +19,7 @@ CSRC = PKG / "csrc"
 SUFFIX = os.environ.get("FEMTC_LIB_SUFFIX", "")
 OBJ = CSRC / ("_obj" + SUFFIX)
 LIB = PKG / f"libfemtc_b200{SUFFIX}.so"
-SOURCES = ["api.cu", "generic_kernels.cu", "tiled_kernels.cu", "column_kernels.cu", "cell_kernels.cu", "tc_kernels.cu", "tmm_kernels.cu"]
+SOURCES = ["api.cu", "generic_kernels.cu", "tiled_kernels.cu", "column_kernels.cu", "cell_kernels.cu", "tc_kernels.cu", "tf32_kernels.cu", "tmm_kernels.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

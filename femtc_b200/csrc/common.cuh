@@ -120,6 +120,8 @@ template <typename T>
 int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
                         int centred, cudaStream_t s);
 
+// tf32_kernels.cu -- tcgen05.mma kind::tf32 arm (fp32 mass n1 = 8), selected with option tc = 1; same convention
+long long launch_mass_tf32(const MassArgs<float>& a);
 int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, int reads, cudaStream_t s);
 
 // tiled_kernels.cu -- degrees 1..8, TMA-staged warp tiles.  Return value:

@@ -650,7 +650,8 @@ long long launch_mass_tc(const MassArgs<T>& a)
       return 0;
     return run_tc_n1<TC_MASS>(n1, a.phi_host, a.phi_host, a.U, a.W, a.detJ, a.num_cells, a.stream);
   }
-  return 0;
+  else
+    return launch_mass_tf32(a); // fp32: tcgen05 kind::tf32 arm (tf32_kernels.cu), option tc = 1
 }
 
 template <typename T>

@@ -653,20 +653,45 @@ def test_forward_interpolation_operator_matches_oracle(femtc, oracle, torch_cuda
 # tc: 1 = DMMA tensor-core family wherever applicable (fp64, degrees 5..8, mass / REF_EXACT), 0 = never.
 # variant 9 = cell family (one thread per cell, degrees 1..2) off -> slab / column kernels serve those shapes;
 # variants 1, 2 = alternative pipeline depths of the cell and tensor-core families.
+@pytest.mark.parametrize("dt", DTYPES)
 @pytest.mark.parametrize("tc", (0, 1))
 @pytest.mark.parametrize("P", (5, 6, 7, 8))
 @pytest.mark.parametrize("op", ("mass", "stiffness"))
-def test_tensor_core_family_parity(femtc, oracle, torch_cuda, op, P, tc):
+def test_tensor_core_family_parity(femtc, oracle, torch_cuda, op, P, tc, dt):
+    """fp64: the DMMA family; fp32: the tcgen05 kind::tf32 arm (three-product split; serves mass at degree 7, every
+    other fp32 shape falls through to the FMA kernels) -- both against the oracle at the dtype's tolerance."""
     nc = {5: 263, 6: 131, 7: 68, 8: 37}[P]  # odd counts: the skewed-copy families leave one cell to the tail kernel
     femtc.set_option("tc", tc)
     try:
+        if dt == "float32" and tc == 1:
+            fam = femtc.kernel_info(op, 4, P, 0)["family"]
+            assert (fam == 4) == (op == "mass" and P == 7), (op, P, fam)
         for centred in (False, True):
-            phi, U, geom = splitmix(oracle, op, P, nc, "float64", seed=77 + P, centred=centred)
+            phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=77 + P, centred=centred)
             ref = oracle_run(oracle, op, phi, U, geom, P, 0)
             W = run_device(femtc, torch_cuda, op, phi, U, geom, P, 0)
             assert np.isfinite(W).all()
             err = rel_err(W, ref) if centred else elementwise_rel_err(W, ref)
-            assert err <= TOL["float64"], (op, P, tc, centred, err)
+            assert err <= TOL[dt], (op, P, tc, centred, err)
+    finally:
+        femtc.set_option("tc", -1)
+
+
+def test_tf32_tensor_core_arm_many_tiles(femtc, oracle, torch_cuda):
+    """The tcgen05 arm on a batch that gives every block several tiles (ring refills, TMEM reuse, both parities of the
+    mbarriers) plus a ragged tail; error of the three-product TF32 split reported against the fp32 tolerance."""
+    P, nc = 7, 148 * 16 * 2 * 5 + 3
+    femtc.set_option("tc", 1)
+    try:
+        for centred in (False, True):
+            phi, U, geom = splitmix(oracle, "mass", P, nc, "float32", seed=5, centred=centred)
+            ref = oracle_run(oracle, "mass", phi, U, geom, P, 0)
+            W = run_device(femtc, torch_cuda, "mass", phi, U, geom, P, 0)
+            err = rel_err(W, ref) if centred else elementwise_rel_err(W, ref)
+            assert err <= TOL["float32"], (centred, err)
+        femtc.set_option("tc", 0)
+        W_fma = run_device(femtc, torch_cuda, "mass", phi, U, geom, P, 0)
+        assert rel_err(W, W_fma) <= TOL["float32"]
     finally:
         femtc.set_option("tc", -1)
 
