@@ -34,6 +34,8 @@ def _load() -> C.CDLL:
         getattr(lib, f"femtc_stiffness_apply_{s}").argtypes = [vp, sz, vp, vp, vp, sz, i, i, i, i, i]
         getattr(lib, f"femtc_mass_apply_device_{s}").argtypes = [vp, sz, vp, vp, vp, sz, i, vp]
         getattr(lib, f"femtc_stiffness_apply_device_{s}").argtypes = [vp, sz, vp, vp, vp, sz, i, i, vp]
+        getattr(lib, f"femtc_mass_apply_device_ex_{s}").argtypes = [vp, sz, vp, vp, vp, sz, i, vp, vp]
+        getattr(lib, f"femtc_stiffness_apply_device_ex_{s}").argtypes = [vp, sz, vp, vp, vp, sz, i, i, vp, vp]
         getattr(lib, f"femtc_gemm_blocked_{s}").argtypes = [i] * 6 + [vp] * 3
         getattr(lib, f"femtc_gemm_micro_{s}").argtypes = [i] * 7 + [vp] * 3
         getattr(lib, f"femtc_gemm_strided_acc_{s}").argtypes = [i] * 8 + [vp] * 3

@@ -153,8 +153,25 @@ static int check_knobs(int degree, int order, int Mb, int Nb)
 
 // ---- device-pointer operators --------------------------------------------------------------------
 template <typename T>
+static int finish_checksum(const T* dW, size_t num_cells, size_t nd, size_t done, double* partials, int count,
+                           double* d_out4, cudaStream_t stream)
+{
+  // `count` triples cover the first `done` cells (0: the kernel family has no fused epilogue); the rest of W -- the
+  // ragged tail, or everything -- goes through the stand-alone first stage, then one second stage sums all triples
+  const size_t covered = count > 0 ? done : 0;
+  int rc = FEMTC_OK;
+  if (covered < num_cells)
+  {
+    if ((rc = launch_checksum_stage1<T>(dW + covered * nd, (num_cells - covered) * nd, partials + 3 * count, stream)))
+      return rc;
+    count += kChecksumStage1Triples;
+  }
+  return launch_checksum_stage2(partials, count, num_cells * nd, d_out4, stream);
+}
+
+template <typename T>
 static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T* ddetJ,
-                       size_t num_cells, int degree, cudaStream_t stream)
+                       size_t num_cells, int degree, cudaStream_t stream, double* d_checksum4 = nullptr)
 {
   NvtxRange nvtx(region<T>("massd:enqueue", "massf:enqueue"));
   if (degree < 1 || degree > 25)
@@ -177,6 +194,14 @@ static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T
   if (rc)
     return rc;
   MassArgs<T> a{phi, dU, dW, ddetJ, num_cells, degree, stream};
+  double* partials = nullptr;
+  int cs_count = 0;
+  if (d_checksum4 && !dry_run())
+  {
+    if ((rc = checksum_scratch(&partials)))
+      return rc;
+    a.cs_partials = partials, a.cs_capacity = kChecksumFused, a.cs_count = &cs_count;
+  }
   size_t done = 0;
   const long long force = g_opt_kernel.load();
   if (force != 1 && degree <= 8)
@@ -203,6 +228,8 @@ static int mass_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T
     MassArgs<T> t{phi, dU + done * nd, dW + done * nd, ddetJ + done * nd, num_cells - done, degree, stream};
     rc = launch_mass_generic<T>(t);
   }
+  if (rc == FEMTC_OK && partials)
+    rc = finish_checksum<T>(dW, num_cells, n2 * (degree + 1), done, partials, cs_count, d_checksum4, stream);
   return rc;
 }
 
@@ -210,7 +237,7 @@ static std::once_flag g_short_phi_once;
 
 template <typename T>
 static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, const T* dG,
-                            size_t num_cells, int degree, int mode, cudaStream_t stream)
+                            size_t num_cells, int degree, int mode, cudaStream_t stream, double* d_checksum4 = nullptr)
 {
   NvtxRange nvtx(region<T>("stiffnessd:enqueue", "stiffnessf:enqueue"));
   if (degree < 1 || degree > 25)
@@ -250,6 +277,14 @@ static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, co
   if (rc)
     return rc;
   StiffnessArgs<T> a{A, D, dU, dW, dG, num_cells, degree, mode, stream};
+  double* partials = nullptr;
+  int cs_count = 0;
+  if (d_checksum4 && !dry_run())
+  {
+    if ((rc = checksum_scratch(&partials)))
+      return rc;
+    a.cs_partials = partials, a.cs_capacity = kChecksumFused, a.cs_count = &cs_count;
+  }
   size_t done = 0;
   const long long force = g_opt_kernel.load();
   if (force != 1 && degree <= 8)
@@ -276,6 +311,8 @@ static int stiffness_device(const T* phi, size_t phi_len, const T* dU, T* dW, co
     StiffnessArgs<T> t{A, D, dU + done * nd, dW + done * nd, dG + done * nd * 6, num_cells - done, degree, mode, stream};
     rc = launch_stiffness_generic<T>(t);
   }
+  if (rc == FEMTC_OK && partials)
+    rc = finish_checksum<T>(dW, num_cells, n2 * (degree + 1), done, partials, cs_count, d_checksum4, stream);
   return rc;
 }
 
@@ -966,6 +1003,27 @@ int femtc_stiffness_apply_device_f32(const float* phi, size_t phi_len, const flo
                                      const float* dG, size_t num_cells, int degree, int mode, void* stream)
 {
   return stiffness_device<float>(phi, phi_len, dU, dW, dG, num_cells, degree, mode, (cudaStream_t)stream);
+}
+
+int femtc_mass_apply_device_ex_f64(const double* phi, size_t phi_len, const double* dU, double* dW, const double* ddetJ,
+                                   size_t num_cells, int degree, double* d_checksum4, void* stream)
+{
+  return mass_device<double>(phi, phi_len, dU, dW, ddetJ, num_cells, degree, (cudaStream_t)stream, d_checksum4);
+}
+int femtc_mass_apply_device_ex_f32(const float* phi, size_t phi_len, const float* dU, float* dW, const float* ddetJ,
+                                   size_t num_cells, int degree, double* d_checksum4, void* stream)
+{
+  return mass_device<float>(phi, phi_len, dU, dW, ddetJ, num_cells, degree, (cudaStream_t)stream, d_checksum4);
+}
+int femtc_stiffness_apply_device_ex_f64(const double* phi, size_t phi_len, const double* dU, double* dW, const double* dG,
+                                        size_t num_cells, int degree, int mode, double* d_checksum4, void* stream)
+{
+  return stiffness_device<double>(phi, phi_len, dU, dW, dG, num_cells, degree, mode, (cudaStream_t)stream, d_checksum4);
+}
+int femtc_stiffness_apply_device_ex_f32(const float* phi, size_t phi_len, const float* dU, float* dW, const float* dG,
+                                        size_t num_cells, int degree, int mode, double* d_checksum4, void* stream)
+{
+  return stiffness_device<float>(phi, phi_len, dU, dW, dG, num_cells, degree, mode, (cudaStream_t)stream, d_checksum4);
 }
 
 int femtc_gemm_blocked_f64(int k, int m, int n, int order, int MB, int NB, const double* a, const double* b, double* c)

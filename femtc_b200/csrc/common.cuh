@@ -85,6 +85,12 @@ struct MassArgs
   size_t num_cells;
   int degree;
   cudaStream_t stream;
+  // checksum fused into the epilogue (femtc_*_apply_device_ex): a launcher whose kernel family supports it leaves one
+  // {sum, sum of squares, max |w|} triple per warp in cs_partials (room for cs_capacity triples) and their number in
+  // *cs_count; a family that does not leaves *cs_count at 0 and the caller reduces W with the stand-alone kernel
+  double* cs_partials = nullptr;
+  int cs_capacity = 0;
+  int* cs_count = nullptr;
 };
 
 template <typename T>
@@ -99,6 +105,9 @@ struct StiffnessArgs
   int degree;
   int mode;
   cudaStream_t stream;
+  double* cs_partials = nullptr; // see MassArgs
+  int cs_capacity = 0;
+  int* cs_count = nullptr;
 };
 
 // generic_kernels.cu -- any degree 1..25, any alignment
@@ -116,6 +125,14 @@ int launch_apply_contractions(int Na, int Nb, int Tr, const T* dI0, const T* dI1
                               const T* dB, T* dA, size_t batch, cudaStream_t s);
 template <typename T>
 int launch_checksum(const T* dX, size_t n, double* d_out4, cudaStream_t s);
+// pieces of it, for the operators' fused checksum (api.cu): the per-device scratch holds kChecksumFused triples for
+// operator kernels, then the kChecksumBlocks triples launch_checksum_stage1 writes; stage 2 sums any number of triples
+constexpr int kChecksumFused = 16384;
+constexpr int kChecksumStage1Triples = 1184;
+int checksum_scratch(double** partials);
+template <typename T>
+int launch_checksum_stage1(const T* dX, size_t n, double* partials, cudaStream_t s);
+int launch_checksum_stage2(const double* partials, int ntriples, size_t n, double* d_out4, cudaStream_t s);
 template <typename T>
 int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint64_t offset,
                         int centred, cudaStream_t s);

@@ -242,8 +242,10 @@ apply_contractions_kernel(int Na, int Nb, int Tr, const T* __restrict__ I0,
 }
 
 // ---- checksum: deterministic two-stage reduction ----------------------------------------------
-constexpr int kChecksumBlocks = 1184; // 148 SMs x 8
-__device__ double g_checksum_partials[kChecksumBlocks * 3];
+constexpr int kChecksumBlocks = kChecksumStage1Triples; // 148 SMs x 8
+// per device: [0, kChecksumFused) triples written by operator kernels with a fused checksum epilogue (one per warp),
+// then kChecksumBlocks triples of the stand-alone first stage
+__device__ double g_checksum_partials[(kChecksumFused + kChecksumBlocks) * 3];
 
 template <typename T>
 __global__ void __launch_bounds__(256) checksum_stage1(const T* __restrict__ x, size_t n, double* partials)
@@ -499,18 +501,42 @@ int launch_apply_contractions(int Na, int Nb, int Tr, const T* dI0, const T* dI1
   return FEMTC_OK;
 }
 
+// The partials buffer is per device and reused: calls on one device must be stream-ordered with respect to each other
+// (they are in every use this library makes of it).
+int checksum_scratch(double** partials)
+{
+  FEMTC_CUDA(cudaGetSymbolAddress((void**)partials, g_checksum_partials));
+  return FEMTC_OK;
+}
+
+template <typename T>
+int launch_checksum_stage1(const T* dX, size_t n, double* partials, cudaStream_t s)
+{
+  checksum_stage1<T><<<kChecksumBlocks, 256, 0, s>>>(dX, n, partials);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
+int launch_checksum_stage2(const double* partials, int ntriples, size_t n, double* d_out4, cudaStream_t s)
+{
+  checksum_stage2<<<1, 256, 0, s>>>(partials, ntriples, n, d_out4);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
 template <typename T>
 int launch_checksum(const T* dX, size_t n, double* d_out4, cudaStream_t s)
 {
-  // The partials buffer is per device and reused: calls on one device must be stream-ordered
-  // with respect to each other (they are in every use this library makes of it).
   double* partials = nullptr;
-  FEMTC_CUDA(cudaGetSymbolAddress((void**)&partials, g_checksum_partials));
-  checksum_stage1<T><<<kChecksumBlocks, 256, 0, s>>>(dX, n, partials);
-  checksum_stage2<<<1, 256, 0, s>>>(partials, kChecksumBlocks, n, d_out4);
-  count_launch(2);
-  FEMTC_CUDA(cudaGetLastError());
-  return FEMTC_OK;
+  int rc = checksum_scratch(&partials);
+  if (rc)
+    return rc;
+  partials += 3 * kChecksumFused;
+  if ((rc = launch_checksum_stage1<T>(dX, n, partials, s)))
+    return rc;
+  return launch_checksum_stage2(partials, kChecksumBlocks, n, d_out4, s);
 }
 
 template <typename T>
@@ -579,6 +605,7 @@ int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, 
   template int launch_apply_contractions<T>(int, int, int, const T*, const T*, const T*, const T*, \
                                             T*, size_t, cudaStream_t);                             \
   template int launch_checksum<T>(const T*, size_t, double*, cudaStream_t);                        \
+  template int launch_checksum_stage1<T>(const T*, size_t, double*, cudaStream_t);                 \
   template int launch_fill_uniform<T>(T*, size_t, uint64_t, uint64_t, uint64_t, int, cudaStream_t);
 INSTANTIATE(double)
 INSTANTIATE(float)

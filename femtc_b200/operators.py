@@ -74,9 +74,12 @@ def _current_stream():
     return torch.cuda.current_stream().cuda_stream
 
 
-def mass_operator(phi, U, W, detJ, num_cells: int, degree: int, order=Order.ijk, Mb: int = 0, Nb: int = 0) -> int:
+def mass_operator(phi, U, W, detJ, num_cells: int, degree: int, order=Order.ijk, Mb: int = 0, Nb: int = 0,
+                  checksum=None) -> int:
     """operators::mass_operator<T>(phi, U, W, detJ, num_cells, degree, order, Mb, Nb)
-    (reference src/mass.hpp:196-199).  W = (AxAxA) diag(detJ) (AxAxA) U per cell."""
+    (reference src/mass.hpp:196-199).  W = (AxAxA) diag(detJ) (AxAxA) U per cell.
+    `checksum` (device path only): a float64 CUDA tensor of 4 values that receives {sum, sum of squares, max |w|, n}
+    of W from the operator's own epilogue (femtc_mass_apply_device_ex_*)."""
     phi = _phi_host(phi)
     s = _suffix_np(phi.dtype)
     _check_sizes(num_cells, degree, (U, "U", 1), (W, "W", 1), (detJ, "detJ", 1))
@@ -86,9 +89,14 @@ def mass_operator(phi, U, W, detJ, num_cells: int, degree: int, order=Order.ijk,
         rc = _knob_code(degree, order, Mb, Nb)
         if rc:
             return _finish(rc)
-        rc = getattr(_lib.lib, f"femtc_mass_apply_device_{s}")(
-            phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(detJ, "detJ", s),
-            int(num_cells), int(degree), _current_stream())
+        if checksum is not None:
+            rc = getattr(_lib.lib, f"femtc_mass_apply_device_ex_{s}")(
+                phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(detJ, "detJ", s),
+                int(num_cells), int(degree), _checksum_ptr(checksum), _current_stream())
+        else:
+            rc = getattr(_lib.lib, f"femtc_mass_apply_device_{s}")(
+                phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(detJ, "detJ", s),
+                int(num_cells), int(degree), _current_stream())
     elif not any(dev):
         rc = getattr(_lib.lib, f"femtc_mass_apply_{s}")(
             phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(detJ, "detJ", s),
@@ -98,8 +106,15 @@ def mass_operator(phi, U, W, detJ, num_cells: int, degree: int, order=Order.ijk,
     return _finish(rc)
 
 
+def _checksum_ptr(x):
+    import torch
+    if not (_is_device(x) and x.dtype == torch.float64 and x.numel() >= 4 and x.is_contiguous()):
+        raise TypeError("checksum: contiguous float64 CUDA tensor of 4 values required")
+    return x.data_ptr()
+
+
 def stiffness_operator(phi, U, W, G, num_cells: int, degree: int, order=Order.ijk, Mb: int = 0, Nb: int = 0,
-                       mode: int = REF_EXACT) -> int:
+                       mode: int = REF_EXACT, checksum=None) -> int:
     """operators::stiffness_operator<T>(phi, U, W, G, num_cells, degree, order, Mb, Nb)
     (reference src/stiffness.hpp:245-248).  mode=REF_EXACT reproduces the reference as coded,
     mode=FULL the intended x+y+z operator (see include/femtc_b200.h)."""
@@ -111,9 +126,14 @@ def stiffness_operator(phi, U, W, G, num_cells: int, degree: int, order=Order.ij
         rc = _knob_code(degree, order, Mb, Nb)
         if rc:
             return _finish(rc)
-        rc = getattr(_lib.lib, f"femtc_stiffness_apply_device_{s}")(
-            phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(G, "G", s),
-            int(num_cells), int(degree), int(mode), _current_stream())
+        if checksum is not None:
+            rc = getattr(_lib.lib, f"femtc_stiffness_apply_device_ex_{s}")(
+                phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(G, "G", s),
+                int(num_cells), int(degree), int(mode), _checksum_ptr(checksum), _current_stream())
+        else:
+            rc = getattr(_lib.lib, f"femtc_stiffness_apply_device_{s}")(
+                phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(G, "G", s),
+                int(num_cells), int(degree), int(mode), _current_stream())
     elif not any(dev):
         rc = getattr(_lib.lib, f"femtc_stiffness_apply_{s}")(
             phi.ctypes.data, phi.size, _ptr(U, "U", s), _ptr(W, "W", s), _ptr(G, "G", s),

@@ -102,6 +102,25 @@ int femtc_stiffness_apply_device_f32(const float* phi_host, size_t phi_len, cons
                                      float* dW, const float* dG, size_t num_cells, int degree,
                                      int mode, void* stream);
 
+/* Same, with the checksum of W produced by the operator itself: d_checksum4 (DEVICE pointer to 4 doubles, may be
+ * NULL) receives {sum, sum of squares, max |w|, n} of the whole W on the same stream -- what the reference's benches
+ * reduce after their timed loop (bench_mass.cpp:135-137: three MPI_Reduce of per-rank figures; here the per-GPU four
+ * are combined by one all-gather, femtc_b200/distributed.py).  The slab kernels (degrees 1..4) accumulate it in their
+ * epilogue from the W values they hold in registers, one partial per warp, without reading W again; other kernel
+ * families and the ragged tail fall back to the stand-alone reduction (femtc_checksum_device_*).  A second-stage kernel
+ * sums the partials in a fixed order: deterministic for a given batch size, equal to femtc_checksum_device_* to
+ * rounding.  Calls on one device must be stream-ordered with respect to each other (one scratch buffer per device). */
+int femtc_mass_apply_device_ex_f64(const double* phi_host, size_t phi_len, const double* dU, double* dW,
+                                   const double* ddetJ, size_t num_cells, int degree, double* d_checksum4, void* stream);
+int femtc_mass_apply_device_ex_f32(const float* phi_host, size_t phi_len, const float* dU, float* dW,
+                                   const float* ddetJ, size_t num_cells, int degree, double* d_checksum4, void* stream);
+int femtc_stiffness_apply_device_ex_f64(const double* phi_host, size_t phi_len, const double* dU, double* dW,
+                                        const double* dG, size_t num_cells, int degree, int mode, double* d_checksum4,
+                                        void* stream);
+int femtc_stiffness_apply_device_ex_f32(const float* phi_host, size_t phi_len, const float* dU, float* dW,
+                                        const float* dG, size_t num_cells, int degree, int mode, double* d_checksum4,
+                                        void* stream);
+
 /* ---- operator handle: geometry resident in HBM (set up once, apply many) ---------------
  * The reference's drivers apply the operator nreps times to the SAME detJ / G
  * (bench_mass.cpp:95-105, bench_stiffness.cpp:95-105); in a matrix-free solver these arrays are

@@ -242,6 +242,44 @@ def test_host_chunking_does_not_change_a_bit(femtc, oracle, torch_cuda, op, mode
     assert elementwise_rel_err(host, oracle_run(oracle, op, phi, U, geom, P, mode)) <= TOL[dt]
 
 
+@pytest.mark.parametrize("op,mode,P,dt,nc", [("stiffness", 0, 3, "float64", 50_003), ("stiffness", 1, 3, "float64", 20_001),
+                                              ("mass", 0, 4, "float32", 30_007), ("mass", 0, 1, "float64", 100_001),
+                                              ("stiffness", 0, 2, "float32", 40_003), ("mass", 0, 6, "float64", 2_005),
+                                              ("stiffness", 0, 7, "float32", 1_003), ("mass", 0, 10, "float64", 301),
+                                              ("stiffness", 0, 3, "float64", 5)])
+def test_checksum_from_the_operator_epilogue(femtc, oracle, torch_cuda, op, mode, P, dt, nc):
+    """femtc_*_apply_device_ex: {sum, sum of squares, max |w|, n} of W from the operator's own launch (slab kernels: per-warp
+    partials from registers; other families and the ragged tail: the stand-alone reduction) equals the stand-alone
+    checksum of W to rounding, is deterministic, and W itself is the plain call's bit for bit."""
+    from femtc_b200.distributed import device_checksum
+    torch = torch_cuda
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=31, centred=(nc % 2 == 0))
+    dU, dg = torch.from_numpy(U).cuda(), torch.from_numpy(geom).cuda()
+    W0 = torch.full_like(dU, float("nan"))
+    W1 = torch.full_like(dU, float("nan"))
+
+    def apply(W, cs):
+        rc = (femtc.mass_operator(phi, dU, W, dg, nc, P, checksum=cs) if op == "mass"
+              else femtc.stiffness_operator(phi, dU, W, dg, nc, P, mode=mode, checksum=cs))
+        assert rc == 0
+    apply(W0, None)
+    got = []
+    for _ in range(3):
+        cs = torch.full((4,), float("nan"), dtype=torch.float64, device="cuda")
+        apply(W1, cs)
+        got.append(cs.cpu().numpy())
+    torch.cuda.synchronize()
+    assert torch.equal(W0.view(torch.uint8), W1.view(torch.uint8))
+    assert np.array_equal(got[0], got[1]) and np.array_equal(got[0], got[2])          # deterministic
+    want = device_checksum(W0).cpu().numpy()
+    assert got[0][3] == want[3] == nc * (P + 1) ** 3 and got[0][2] == want[2]
+    scale = float(np.abs(W0.cpu().numpy().astype(np.float64)).sum())
+    assert abs(got[0][0] - want[0]) <= 1e-12 * scale
+    assert abs(got[0][1] - want[1]) <= 1e-12 * want[1]
+    host = oracle.checksum(W0.cpu().numpy())
+    assert abs(got[0][0] - host[0]) <= 1e-11 * scale and got[0][2] == host[2]
+
+
 def test_kernel_info_reports_the_family_that_serves_each_shape(femtc):
     """femtc_kernel_info walks the real dispatcher in a dry run: nothing is launched, the record names the family."""
     launches0 = femtc.get_option("launches")

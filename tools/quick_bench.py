@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--max-gb", type=float, default=60.0)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--fixed", action="store_true", help="exactly --warmup + --reps launches per configuration (for ncu)")
     ap.add_argument("--tc", type=int, default=-1, help="tensor-core family: 0 off, 1 on, -1 library default")
     ap.add_argument("--configs", default="", help="explicit list op:dtype:P:mode[,...] instead of the cross product")
     a = ap.parse_args()
@@ -95,9 +96,9 @@ def sweep(a, ops, dtypes, degrees, modes):
                         e1.record()
                         torch.cuda.synchronize()
                         per = max(e0.elapsed_time(e1) / a.warmup, 1e-3)
-                        for _ in range(min(2000, int(30.0 / per))):
+                        for _ in range(0 if a.fixed else min(2000, int(30.0 / per))):
                             run()
-                        reps = max(a.reps, min(2000, int(20.0 / per)))
+                        reps = a.reps if a.fixed else max(a.reps, min(2000, int(20.0 / per)))
                         torch.cuda.synchronize()
                         e0.record()
                         for _ in range(reps):
