@@ -10,6 +10,7 @@
 // so three sweeps walk the three axes and come back to the natural index order.
 #include "common.cuh"
 
+#include <algorithm>
 #include <mutex>
 #include <set>
 #include <utility>
@@ -54,12 +55,28 @@ __device__ __forceinline__ void load_matrix(T* dst, const T* __restrict__ src, i
     dst[t] = src[t];
 }
 
+// The 1-D tables of the tuned degrees (n1 <= 9) travel as kernel parameters like in every other family: the ragged tail
+// of a batch then costs one launch and nothing else (no stream-ordered allocation, no pageable host copy), and the whole
+// operator call can be captured in a CUDA graph.  Higher degrees pass a device pointer instead (`phi` != null).
+constexpr int kSmallN1 = 9;
+template <typename T>
+struct SmallTab
+{
+  T a[kSmallN1 * kSmallN1], d[kSmallN1 * kSmallN1];
+};
+template <typename T>
+__device__ __forceinline__ void load_matrix_param(T* dst, const T* src, int n)
+{
+  for (int t = threadIdx.x; t < n; t += blockDim.x)
+    dst[t] = src[t];
+}
+
 // mass.hpp:10-49.  Scratch: 2 buffers of cpb*nd values, in shared memory when `ws` is null,
 // else in the global workspace slice of this block.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-mass_generic_kernel(const T* __restrict__ phi, const T* __restrict__ U, T* __restrict__ W,
-                    const T* __restrict__ detJ, size_t num_cells, int n1, int cpb, T* ws)
+mass_generic_kernel(const T* __restrict__ phi, const __grid_constant__ SmallTab<T> tab, const T* __restrict__ U,
+                    T* __restrict__ W, const T* __restrict__ detJ, size_t num_cells, int n1, int cpb, T* ws)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* A = reinterpret_cast<T*>(smem_raw);
@@ -67,7 +84,10 @@ mass_generic_kernel(const T* __restrict__ phi, const T* __restrict__ U, T* __res
   const size_t nd = (size_t)n2 * n1;
   T* b0 = ws ? ws + (size_t)blockIdx.x * 2 * cpb * nd : A + n2;
   T* b1 = b0 + (size_t)cpb * nd;
-  load_matrix(A, phi, n2);
+  if (phi)
+    load_matrix(A, phi, n2);
+  else
+    load_matrix_param(A, tab.a, n2);
   __syncthreads();
 
   const size_t groups = (num_cells + cpb - 1) / cpb;
@@ -88,7 +108,7 @@ mass_generic_kernel(const T* __restrict__ phi, const T* __restrict__ U, T* __res
 // stiffness.hpp:34-99.  Scratch: 5 buffers of cpb*nd values.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-stiffness_generic_kernel(const T* __restrict__ phiA, const T* __restrict__ phiD,
+stiffness_generic_kernel(const T* __restrict__ phiA, const T* __restrict__ phiD, const __grid_constant__ SmallTab<T> tab,
                          const T* __restrict__ U, T* __restrict__ W, const T* __restrict__ G,
                          size_t num_cells, int n1, int cpb, int mode, T* ws)
 {
@@ -103,8 +123,16 @@ stiffness_generic_kernel(const T* __restrict__ phiA, const T* __restrict__ phiD,
   T* wx = t1 + bs;
   T* wy = wx + bs;
   T* wz = wy + bs;
-  load_matrix(A, phiA, n2);
-  load_matrix(D, phiD, n2);
+  if (phiA)
+  {
+    load_matrix(A, phiA, n2);
+    load_matrix(D, phiD, n2);
+  }
+  else
+  {
+    load_matrix_param(A, tab.a, n2);
+    load_matrix_param(D, tab.d, n2);
+  }
   __syncthreads();
 
   const size_t groups = (num_cells + cpb - 1) / cpb;
@@ -400,15 +428,21 @@ int launch_mass_generic(const MassArgs<T>& a)
   if (dry_run())
     return FEMTC_OK;
   AsyncBuf dphi, ws;
-  int rc = dphi.alloc(n2 * sizeof(T), a.stream);
-  if (rc)
-    return rc;
-  FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.phi_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  SmallTab<T> tab;
+  int rc = FEMTC_OK;
+  if (n1 <= kSmallN1)
+    std::copy(a.phi_host, a.phi_host + n2, tab.a);
+  else
+  {
+    if ((rc = dphi.alloc(n2 * sizeof(T), a.stream)))
+      return rc;
+    FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.phi_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  }
   if (spill && (rc = ws.alloc((size_t)grid * 2 * nd * sizeof(T), a.stream)))
     return rc;
   if ((rc = opt_in_smem(mass_generic_kernel<T>)))
     return rc;
-  mass_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), a.U, a.W, a.detJ, a.num_cells, n1, cpb,
+  mass_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), tab, a.U, a.W, a.detJ, a.num_cells, n1, cpb,
                                                              ws.as<T>());
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
@@ -437,17 +471,26 @@ int launch_stiffness_generic(const StiffnessArgs<T>& a)
   if (dry_run())
     return FEMTC_OK;
   AsyncBuf dphi, ws;
-  int rc = dphi.alloc(2 * n2 * sizeof(T), a.stream);
-  if (rc)
-    return rc;
-  FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.A_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
-  FEMTC_CUDA(cudaMemcpyAsync(dphi.as<T>() + n2, a.D_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  SmallTab<T> tab;
+  int rc = FEMTC_OK;
+  if (n1 <= kSmallN1)
+  {
+    std::copy(a.A_host, a.A_host + n2, tab.a);
+    std::copy(a.D_host, a.D_host + n2, tab.d);
+  }
+  else
+  {
+    if ((rc = dphi.alloc(2 * n2 * sizeof(T), a.stream)))
+      return rc;
+    FEMTC_CUDA(cudaMemcpyAsync(dphi.p, a.A_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+    FEMTC_CUDA(cudaMemcpyAsync(dphi.as<T>() + n2, a.D_host, n2 * sizeof(T), cudaMemcpyHostToDevice, a.stream));
+  }
   if (spill && (rc = ws.alloc((size_t)grid * 5 * nd * sizeof(T), a.stream)))
     return rc;
   if ((rc = opt_in_smem(stiffness_generic_kernel<T>)))
     return rc;
-  stiffness_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), dphi.as<T>() + n2, a.U, a.W, a.G,
-                                                                  a.num_cells, n1, cpb, a.mode, ws.as<T>());
+  stiffness_generic_kernel<T><<<grid, kThreads, smem, a.stream>>>(dphi.as<T>(), dphi.p ? dphi.as<T>() + n2 : nullptr, tab,
+                                                                  a.U, a.W, a.G, a.num_cells, n1, cpb, a.mode, ws.as<T>());
   count_launch();
   FEMTC_CUDA(cudaGetLastError());
   return FEMTC_OK;
