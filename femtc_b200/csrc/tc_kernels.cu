@@ -108,8 +108,18 @@ struct TcPlan
   static constexpr int off_j = off_u + stage_bytes;
   static constexpr int off_e = off_j + (OP == TC_MASS ? stage_bytes : 0);
   static constexpr int off_g = off_e + 3 * e_bytes;
-  static constexpr int off_bar = off_g + (OP == TC_STIFF ? NW * NGS * g_slot_bytes : 0);
-  static constexpr int smem_bytes = (off_bar + 16 + 127) & ~127;
+  // NGS >= 100: geometry in GST = NGS - 100 block-wide stages that hold a WHOLE cell each, filled by n1 bulk copies
+  // (one i0-plane = n2 records = 3 n2 16-byte units; planes are pitched to an odd number of units so that the 128-bit
+  // reads of a quarter-warp -- two planes x four column pairs 6 units apart -- fall into eight different bank groups).
+  // The cp.async rings cost 11.5 shared-memory wavefronts per 512-byte instruction (sectors land one by one) and were
+  // 40 % of all wavefronts of the n1 = 7 kernel (profiles/r02_ncu_tc_stiffness_before.txt).
+  static constexpr bool GB = NGS >= 100;
+  static constexpr int GST = GB ? NGS - 100 : 0;
+  static constexpr int gb_plane_bytes = N2 * 48;
+  static constexpr int gb_pitch = 16 * ((3 * N2) % 2 ? 3 * N2 : 3 * N2 + 1);
+  static constexpr int gb_stage_bytes = (N1 * gb_pitch + 127) & ~127;
+  static constexpr int off_bar = off_g + (OP == TC_STIFF ? (GB ? GST * gb_stage_bytes : NW * NGS * g_slot_bytes) : 0);
+  static constexpr int smem_bytes = (off_bar + 16 + 8 * GST + 127) & ~127;
   static constexpr int g_chunks = N1 * (g_piece_bytes / 16);  // 16-byte chunks of one tile's geometry
   static constexpr int g_nj = (g_chunks + 31) / 32;           // cp.async per lane and tile
 };
@@ -232,10 +242,13 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
   // zero everything once: padded planes / k-steps are multiplied by zero table entries and must be finite
   for (int i = tid; i < PL::off_bar / 16; i += 32 * NW)
     reinterpret_cast<float4*>(smem)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const uint32_t barG = barJ + 8; // whole-cell geometry stages (PL::GB)
   if (tid == 0)
   {
     mbar_init(barU, 1);
     mbar_init(barJ, 1);
+    for (int i = 0; i < PL::GST; ++i)
+      mbar_init(barG + 8 * i, 1);
     fence_mbar_init();
   }
   fence_proxy_async(); // the zero fill (generic proxy) is ordered before the first bulk copies (async proxy)
@@ -294,14 +307,36 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     tc_cp_commit(); // one group per tile, also when nothing is left to request: keeps the group count uniform
   };
 
+  // whole-cell geometry stage: n1 bulk copies, one per i0-plane, completing on the stage's barrier
+  auto load_cell_g = [&](long long c, int stage)
+  {
+    if (tid == 0)
+    {
+      mbar_expect_tx(barG + 8 * stage, N1 * PL::gb_plane_bytes);
+      const unsigned char* src = reinterpret_cast<const unsigned char*>(Gm + (size_t)c * ND * 6);
+      const uint32_t dst = smem_u32(smem + PL::off_g + stage * PL::gb_stage_bytes);
+#pragma unroll
+      for (int i0 = 0; i0 < N1; ++i0)
+        bulk_g2s(dst + i0 * PL::gb_pitch, src + (size_t)i0 * PL::gb_plane_bytes, PL::gb_plane_bytes, barG + 8 * stage);
+    }
+  };
+  int gstage = 0;
+  uint32_t gphase = 0;
+
   if (cell < ncells)
   {
     load_cell(U, uS, barU, cell);
     if constexpr (OP == TC_MASS)
       load_cell(Gm, jS, barJ, cell);
   }
+  if constexpr (OP == TC_STIFF && PL::GB)
+  {
+    for (int i = 0; i < PL::GST; ++i)
+      if (cell + i * stride < ncells)
+        load_cell_g(cell + i * stride, i);
+  }
   int slot = 0; // ring slot of the next tile to consume
-  if constexpr (OP == TC_STIFF)
+  if constexpr (OP == TC_STIFF && !PL::GB)
   {
 #pragma unroll
     for (int i = 0; i < NGS - 1; ++i)
@@ -355,6 +390,8 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     // fragment (g, t) of a tile holds the points (i0 = g, col = c0 + 2t, c0 + 2t + 1), col = (a1, a2) flattened
     if constexpr (OP == TC_MASS)
       mbar_wait(barJ, phase);
+    if constexpr (OP == TC_STIFF && PL::GB)
+      mbar_wait(barG + 8 * gstage, gphase);
     {
       const double* jc = jS + sk; // mass: detJ in natural order
 #pragma unroll
@@ -420,13 +457,24 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
             dmma(wy2, FA2.a0, bd0);  dmma(wy2, FA2.a1, bd1);
           }
           // geometry (stiffness.hpp:14-29); only f2 is observable in REF_EXACT
-          load_tile_g();              // the tile NGS - 1 ahead, into the slot freed by the previous tile
-          tc_cp_wait<NGS - 1>();      // this lane's chunks of the current tile have landed ...
-          __syncwarp();               // ... and so have everybody else's
-          const unsigned char* sl = gRing + slot * PL::g_slot_bytes;
+          const unsigned char* sl;
+          int pitch;
+          if constexpr (PL::GB)
+          {
+            sl = smem + PL::off_g + gstage * PL::gb_stage_bytes + c0 * 48; // the tile's first record of plane 0
+            pitch = PL::gb_pitch;
+          }
+          else
+          {
+            load_tile_g();              // the tile NGS - 1 ahead, into the slot freed by the previous tile
+            tc_cp_wait<(PL::GB ? 0 : NGS - 1)>(); // this lane's chunks of the current tile have landed ...
+            __syncwarp();               // ... and so have everybody else's
+            sl = gRing + slot * PL::g_slot_bytes;
+            pitch = PL::g_plane_pitch;
+          }
           if (N1 >= 8 || g < N1)
           {
-            const double* r = reinterpret_cast<const double*>(sl + g * PL::g_plane_pitch) + 12 * t;
+            const double* r = reinterpret_cast<const double*>(sl + g * pitch) + 12 * t;
             const double2 p0 = *reinterpret_cast<const double2*>(r);
             const double2 p1 = *reinterpret_cast<const double2*>(r + 2);
             const double2 p3 = *reinterpret_cast<const double2*>(r + 6);
@@ -442,7 +490,7 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
           {
             if (g == 0)
             {
-              const double* r = reinterpret_cast<const double*>(sl + 8 * PL::g_plane_pitch) + 12 * t;
+              const double* r = reinterpret_cast<const double*>(sl + 8 * pitch) + 12 * t;
               const double2 p0 = *reinterpret_cast<const double2*>(r);
               const double2 p1 = *reinterpret_cast<const double2*>(r + 2);
               const double2 p3 = *reinterpret_cast<const double2*>(r + 6);
@@ -455,8 +503,11 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
                 E0[8 * S + cp] = f0, E0[8 * S + cp + 1] = f1;
             }
           }
-          __syncwarp(); // every lane is done with this slot before the next tile's request overwrites it
-          slot = (slot + 1 == NGS) ? 0 : slot + 1;
+          if constexpr (!PL::GB)
+          {
+            __syncwarp(); // every lane is done with this slot before the next tile's request overwrites it
+            slot = (slot + 1 == NGS) ? 0 : slot + 1;
+          }
         }
       }
     }
@@ -464,6 +515,14 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     if constexpr (OP == TC_MASS)
       if (cn < ncells)
         load_cell(Gm, jS, barJ, cn);
+    if constexpr (OP == TC_STIFF && PL::GB)
+    {
+      // every geometry value of this stage went into an E0 store before the barrier above (tma.cuh, rule 1): refill
+      if (cell + PL::GST * stride < ncells)
+        load_cell_g(cell + PL::GST * stride, gstage);
+      if (++gstage == PL::GST)
+        gstage = 0, gphase ^= 1;
+    }
 
     // ---- backward: axis 0, axis 1, axis 2 ----------------------------------------------------------------------------------
     double* wS; // W staging, natural order (+ skew)
@@ -621,13 +680,27 @@ long long run_tc_n1(int n1, const double* A, const double* D, const double* U, d
   {
     switch (n1)
     {
-    case 6: return run_tc<6, OP, 3, 2>(A, D, U, W, geom, num_cells, stream);
-    case 7: return v == 1 ? run_tc<7, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
-                          : run_tc<7, OP, 3, 4>(A, D, U, W, geom, num_cells, stream);
-    case 8: return v == 1 ? run_tc<8, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
-                          : run_tc<8, OP, 3, 4>(A, D, U, W, geom, num_cells, stream);
-    case 9: return v == 1 ? run_tc<9, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
-                          : run_tc<9, OP, 2, 4>(A, D, U, W, geom, num_cells, stream);
+    case 6: return v == 31 ? run_tc<6, OP, 102, 2>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<6, OP, 102, 5>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<6, OP, 3, 2>(A, D, U, W, geom, num_cells, stream);
+    // Geometry transport (profiles/r02_ab_tc_geometry_stages.txt; % of measured HBM, burst): whole-cell stages filled by
+    // bulk copies replace the per-warp cp.async rings of round 1 (variant 30):  n1 = 7  74.5 -> 87.2 (2 stages; 3: 81.0),
+    // n1 = 8  92.4 -> 102.2 (2),  n1 = 9  67.2 -> 74.2 (1 stage; 2 stages cost a resident block: 66.4).
+    case 7: return v == 1   ? run_tc<7, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
+                 : v == 30 ? run_tc<7, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 31 ? run_tc<7, OP, 103, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<7, OP, 102, 7>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<7, OP, 102, 4>(A, D, U, W, geom, num_cells, stream);
+    case 8: return v == 1   ? run_tc<8, OP, 2, 2>(A, D, U, W, geom, num_cells, stream)
+                 : v == 30 ? run_tc<8, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<8, OP, 102, 8>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<8, OP, 102, 4>(A, D, U, W, geom, num_cells, stream);
+    case 9: return v == 1   ? run_tc<9, OP, 3, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 30 ? run_tc<9, OP, 2, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 31 ? run_tc<9, OP, 102, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<9, OP, 101, 6>(A, D, U, W, geom, num_cells, stream)
+                 : v == 34 ? run_tc<9, OP, 102, 6>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<9, OP, 101, 4>(A, D, U, W, geom, num_cells, stream);
     default: return 0;
     }
   }

@@ -280,6 +280,40 @@ def test_checksum_from_the_operator_epilogue(femtc, oracle, torch_cuda, op, mode
     assert abs(got[0][0] - host[0]) <= 1e-11 * scale and got[0][2] == host[2]
 
 
+@pytest.mark.parametrize("op,P,dt,nc", [("stiffness", 3, "float64", 15625), ("mass", 3, "float64", 15625),
+                                        ("stiffness", 6, "float32", 2915), ("mass", 8, "float64", 1371)])
+def test_operator_call_is_graph_capturable(femtc, oracle, torch_cuda, op, P, dt, nc):
+    """The reference's default problem (run.sh:9: 1e6 DoFs) is a ~10 us launch: a solver would replay it from a CUDA graph.
+    Nothing in a device-pointer call allocates, copies or synchronises (tables are kernel parameters, the ragged tail is
+    one more launch), so stream capture works and a replay with new inputs equals the eager call bit for bit."""
+    torch = torch_cuda
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=3)
+    dU, dg = torch.from_numpy(U).cuda(), torch.from_numpy(geom).cuda()
+    dW = torch.zeros_like(dU)
+
+    def call():
+        rc = femtc.mass_operator(phi, dU, dW, dg, nc, P) if op == "mass" else femtc.stiffness_operator(phi, dU, dW, dg, nc, P)
+        assert rc == 0
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        call()                                   # plans are made (and cached) outside the capture
+        torch.cuda.synchronize()
+        with torch.cuda.graph(graph, stream=side):
+            call()
+    for rep in range(2):
+        dU.mul_(0.5).add_(0.25 * rep)            # new inputs in the captured buffers
+        dW.fill_(float("nan"))
+        graph.replay()
+        torch.cuda.synchronize()
+        replayed = dW.clone()
+        call()
+        torch.cuda.synchronize()
+        assert torch.equal(replayed.view(torch.uint8), dW.view(torch.uint8))
+    ref = oracle_run(oracle, op, phi, dU.cpu().numpy(), geom, P)
+    assert elementwise_rel_err(dW.cpu().numpy(), ref) <= TOL[dt]
+
+
 def test_kernel_info_reports_the_family_that_serves_each_shape(femtc):
     """femtc_kernel_info walks the real dispatcher in a dry run: nothing is launched, the record names the family."""
     launches0 = femtc.get_option("launches")
@@ -713,6 +747,26 @@ def test_tensor_core_family_parity(femtc, oracle, torch_cuda, op, P, tc, dt):
             assert err <= TOL[dt], (op, P, tc, centred, err)
     finally:
         femtc.set_option("tc", -1)
+
+
+@pytest.mark.parametrize("variant", (30, 31, 33, 34))   # cp.async rings of round 1 / other stage counts / other warps per cell
+@pytest.mark.parametrize("P", (5, 6, 7, 8))
+def test_tensor_core_geometry_transport_variants(femtc, oracle, torch_cuda, P, variant):
+    """DMMA stiffness kernels: the geometry transport (whole-cell stages filled by bulk copies, or the per-warp cp.async
+    rings) and the number of warps per cell change no arithmetic -- every variant equals the default bit for bit, and
+    the oracle within tolerance, over enough cells for every block to cycle its stages several times."""
+    nc = 148 * 4 * 5 + 37
+    phi, U, geom = splitmix(oracle, "stiffness", P, nc, "float64", seed=P, centred=True)
+    femtc.set_option("tc", 1)
+    try:
+        base = run_device(femtc, torch_cuda, "stiffness", phi, U, geom, P, 0)
+        femtc.set_option("variant", variant)
+        other = run_device(femtc, torch_cuda, "stiffness", phi, U, geom, P, 0)
+    finally:
+        femtc.set_option("variant", 0)
+        femtc.set_option("tc", -1)
+    assert np.array_equal(base, other)
+    assert rel_err(base, oracle_run(oracle, "stiffness", phi, U, geom, P, 0)) <= TOL["float64"]
 
 
 def test_tf32_tensor_core_arm_many_tiles(femtc, oracle, torch_cuda):
