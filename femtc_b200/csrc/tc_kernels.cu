@@ -35,8 +35,12 @@
 // shared memory is never actually waited for).  Odd n1: cells are 8 bytes short of 16-byte units -> skewed copies as in
 // tiled_kernels.cu (RoundStage, SHIFT).  Every byte crosses HBM once.
 //
-// Semantics follow the reference as coded (REF_EXACT: include/femtc_b200.h).  FULL stays on the
-// column kernels.
+// Semantics follow the reference as coded (REF_EXACT: include/femtc_b200.h).  FULL (the x + y + z operator, round 2):
+//     A2,D2 | A1,D1 ; A1 | D0,A0,A0 + full 3x3 geometry | D0,A0,A0 | A1+D1 ; A1 | A2+D2        (16 GEMMs, 6 exchange buffers)
+// the partial products of the three backward chains are merged as soon as they share the rest of their path.
+//
+// Round 2: the geometry of the stiffness kernels arrives in whole-cell stages filled by n1 bulk copies (TcPlan::GB);
+// the cp.async rings described above remain as variant 30 for A/B.
 #include "common.cuh"
 
 #include <map>
@@ -52,7 +56,7 @@ long long opt_tc();
 
 namespace
 {
-constexpr int TC_MASS = 0, TC_STIFF = 1;
+constexpr int TC_MASS = 0, TC_STIFF = 1, TC_STIFF_FULL = 2; // FULL: the x + y + z operator (include/femtc_b200.h)
 
 __device__ __forceinline__ void tc_cp_async16(uint32_t dst, const void* src)
 {
@@ -106,8 +110,10 @@ struct TcPlan
   static constexpr int g_slot_bytes = N1 * g_plane_pitch;
   static constexpr int off_u = 0;
   static constexpr int off_j = off_u + stage_bytes;
+  static constexpr bool STIFF = OP != TC_MASS, FULL = OP == TC_STIFF_FULL;
+  static constexpr int NE = FULL ? 6 : 3;             // exchange buffers
   static constexpr int off_e = off_j + (OP == TC_MASS ? stage_bytes : 0);
-  static constexpr int off_g = off_e + 3 * e_bytes;
+  static constexpr int off_g = off_e + NE * e_bytes;
   // NGS >= 100: geometry in GST = NGS - 100 block-wide stages that hold a WHOLE cell each, filled by n1 bulk copies
   // (one i0-plane = n2 records = 3 n2 16-byte units; planes are pitched to an odd number of units so that the 128-bit
   // reads of a quarter-warp -- two planes x four column pairs 6 units apart -- fall into eight different bank groups).
@@ -118,7 +124,8 @@ struct TcPlan
   static constexpr int gb_plane_bytes = N2 * 48;
   static constexpr int gb_pitch = 16 * ((3 * N2) % 2 ? 3 * N2 : 3 * N2 + 1);
   static constexpr int gb_stage_bytes = (N1 * gb_pitch + 127) & ~127;
-  static constexpr int off_bar = off_g + (OP == TC_STIFF ? (GB ? GST * gb_stage_bytes : NW * NGS * g_slot_bytes) : 0);
+  static_assert(!FULL || GB, "FULL reads all six geometry values from whole-cell stages");
+  static constexpr int off_bar = off_g + (STIFF ? (GB ? GST * gb_stage_bytes : NW * NGS * g_slot_bytes) : 0);
   static constexpr int smem_bytes = (off_bar + 16 + 8 * GST + 127) & ~127;
   static constexpr int g_chunks = N1 * (g_piece_bytes / 16);  // 16-byte chunks of one tile's geometry
   static constexpr int g_nj = (g_chunks + 31) / 32;           // cp.async per lane and tile
@@ -214,6 +221,61 @@ __device__ __forceinline__ void tc_phase(const double* in, const MFrag (&M)[NM],
   }
 }
 
+// Y = M0 . X0 + M1 . X1: two inputs in the same layout accumulated into one output (the backward sweeps of the
+// FULL operator, where two partial products meet before the next axis).
+template <int N1, int NW, class AIN, class SOUT>
+__device__ __forceinline__ void tc_phase_sum(const double* in0, const double* in1, const MFrag& M0, const MFrag& M1,
+                                             const double* tab0, const double* tab1, AIN ain, SOUT sout, int g, int t,
+                                             int warp, int tid)
+{
+  constexpr int N2 = N1 * N1, NT = (N2 + 7) / 8;
+  constexpr bool R8 = N1 == 9;
+#pragma unroll
+  for (int k = 0; k < (NT + NW - 1) / NW; ++k)
+  {
+    const int tile = warp + k * NW;
+    if ((k + 1) * NW > NT && tile >= NT)
+      break;
+    const int c0 = (8 * tile + 8 <= N2) ? 8 * tile : N2 - 8;
+    const double x0 = in0[ain(t, c0 + g)], x1 = in0[ain(4 + t, c0 + g)];
+    const double y0 = in1[ain(t, c0 + g)], y1 = in1[ain(4 + t, c0 + g)];
+    double acc[2] = {0.0, 0.0};
+    if constexpr (R8)
+    {
+      acc[0] = fma(M1.m8, in1[ain(8, c0 + 2 * t)], M0.m8 * in0[ain(8, c0 + 2 * t)]);
+      acc[1] = fma(M1.m8, in1[ain(8, c0 + 2 * t + 1)], M0.m8 * in0[ain(8, c0 + 2 * t + 1)]);
+    }
+    dmma(acc, M0.a0, x0);
+    dmma(acc, M0.a1, x1);
+    dmma(acc, M1.a0, y0);
+    dmma(acc, M1.a1, y1);
+    if (N1 >= 8 || g < N1)
+    {
+      sout(g, c0 + 2 * t, acc[0]);
+      sout(g, c0 + 2 * t + 1, acc[1]);
+    }
+  }
+  if constexpr (R8)
+  {
+#pragma unroll
+    for (int j = 0; j < (N2 + 32 * NW - 1) / (32 * NW); ++j)
+    {
+      const int col = tid + 32 * NW * j;
+      if (col < N2)
+      {
+        double s = tab0[8] * in0[ain(0, col)];
+#pragma unroll
+        for (int p = 1; p < 9; ++p)
+          s = fma(tab0[8 + 9 * p], in0[ain(p, col)], s);
+#pragma unroll
+        for (int p = 0; p < 9; ++p)
+          s = fma(tab1[8 + 9 * p], in1[ain(p, col)], s);
+        sout(8, col, s);
+      }
+    }
+  }
+}
+
 template <int N1, int OP, int NGS, int NW>
 __global__ void __launch_bounds__(32 * NW)
 tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, double* __restrict__ W,
@@ -221,7 +283,7 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
 {
   using PL = TcPlan<N1, OP, NGS, NW>;
   constexpr int N2 = PL::N2, ND = PL::ND, S = PL::S, NT = PL::NT;
-  constexpr bool R8 = PL::R8;
+  constexpr bool R8 = PL::R8, STIFF = PL::STIFF, FULL = PL::FULL;
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   auto block_sync = [&]()
@@ -236,6 +298,9 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
   double* E0 = reinterpret_cast<double*>(smem + PL::off_e);
   double* E1 = reinterpret_cast<double*>(smem + PL::off_e + PL::e_bytes);
   double* E2 = reinterpret_cast<double*>(smem + PL::off_e + 2 * PL::e_bytes);
+  double* E3 = reinterpret_cast<double*>(smem + PL::off_e + (FULL ? 3 : 0) * PL::e_bytes); // FULL only
+  double* E4 = reinterpret_cast<double*>(smem + PL::off_e + (FULL ? 4 : 0) * PL::e_bytes);
+  double* E5 = reinterpret_cast<double*>(smem + PL::off_e + (FULL ? 5 : 0) * PL::e_bytes);
   unsigned char* gRing = smem + PL::off_g + warp * NGS * PL::g_slot_bytes; // this warp's ring
   const uint32_t barU = smem_u32(smem + PL::off_bar), barJ = barU + 8;
 
@@ -329,14 +394,14 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     if constexpr (OP == TC_MASS)
       load_cell(Gm, jS, barJ, cell);
   }
-  if constexpr (OP == TC_STIFF && PL::GB)
+  if constexpr (STIFF && PL::GB)
   {
     for (int i = 0; i < PL::GST; ++i)
       if (cell + i * stride < ncells)
         load_cell_g(cell + i * stride, i);
   }
   int slot = 0; // ring slot of the next tile to consume
-  if constexpr (OP == TC_STIFF && !PL::GB)
+  if constexpr (STIFF && !PL::GB)
   {
 #pragma unroll
     for (int i = 0; i < NGS - 1; ++i)
@@ -351,14 +416,24 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
 
     // ---- phase A: axis 2.  t2 = A2 u -> E0 as [a1][a0, i2]  (stiffness.hpp:68, mass.hpp:38 order is immaterial) --
     mbar_wait(barU, phase);
-    tc_phase<N1, NW, 1>(
-        uS + sk, FA, tabA, [](int p, int col) { return col * N1 + p; },
-        [&](int, int i, int col, double v)
-        {
-          const int a0 = col / N1, a1 = col - a0 * N1;
-          E0[a1 * S + a0 * N1 + i] = v;
-        },
-        g, t, warp, tid);
+    if constexpr (FULL)
+      tc_phase<N1, NW, 2>(                                   // A2 u -> E0, D2 u -> E3
+          uS + sk, FAD, tabAD, [](int p, int col) { return col * N1 + p; },
+          [&](int m, int i, int col, double v)
+          {
+            const int a0 = col / N1, a1 = col - a0 * N1;
+            (m == 0 ? E0 : E3)[a1 * S + a0 * N1 + i] = v;
+          },
+          g, t, warp, tid);
+    else
+      tc_phase<N1, NW, 1>(
+          uS + sk, FA, tabA, [](int p, int col) { return col * N1 + p; },
+          [&](int, int i, int col, double v)
+          {
+            const int a0 = col / N1, a1 = col - a0 * N1;
+            E0[a1 * S + a0 * N1 + i] = v;
+          },
+          g, t, warp, tid);
     if (tid == 0)
       bulk_wait_read0(); // the previous cell's W store has finished reading its staging (E1 / E2), rewritten below
     block_sync();
@@ -366,7 +441,8 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
       load_cell(U, uS, barU, cn);
 
     // ---- phase B: axis 1.  stiffness: ta = A1 t2 -> E1, td = D1 t2 -> E2; mass: A1 t2 -> E1; layout [a0][i1, a2] ----
-    if constexpr (OP == TC_STIFF)
+    if constexpr (STIFF)
+    {
       tc_phase<N1, NW, 2>(
           E0, FAD, tabAD, [](int p, int col) { return p * S + col; },
           [&](int m, int i, int col, double v)
@@ -375,6 +451,16 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
             (m == 0 ? E1 : E2)[a0 * S + i * N1 + a2] = v;
           },
           g, t, warp, tid);
+      if constexpr (FULL)
+        tc_phase<N1, NW, 1>(                                 // A1 (D2 u) -> E4
+            E3, FA, tabA, [](int p, int col) { return p * S + col; },
+            [&](int, int i, int col, double v)
+            {
+              const int a0 = col / N1, a2 = col - a0 * N1;
+              E4[a0 * S + i * N1 + a2] = v;
+            },
+            g, t, warp, tid);
+    }
     else
       tc_phase<N1, NW, 1>(
           E0, FA, tabA, [](int p, int col) { return p * S + col; },
@@ -390,7 +476,7 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     // fragment (g, t) of a tile holds the points (i0 = g, col = c0 + 2t, c0 + 2t + 1), col = (a1, a2) flattened
     if constexpr (OP == TC_MASS)
       mbar_wait(barJ, phase);
-    if constexpr (OP == TC_STIFF && PL::GB)
+    if constexpr (STIFF && PL::GB)
       mbar_wait(barG + 8 * gstage, gphase);
     {
       const double* jc = jS + sk; // mass: detJ in natural order
@@ -434,26 +520,29 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
         {
           const double ba0 = E1[t * S + c0 + g], ba1 = E1[(4 + t) * S + c0 + g];
           const double bd0 = E2[t * S + c0 + g], bd1 = E2[(4 + t) * S + c0 + g];
+          // the z term: REF_EXACT uses A0 A1 A2 u (stiffness.hpp:76-77 as coded), FULL the real A0 A1 D2 u
+          const double bz0 = FULL ? E4[t * S + c0 + g] : ba0, bz1 = FULL ? E4[(4 + t) * S + c0 + g] : ba1;
           double wx[2] = {0.0, 0.0}, wy[2] = {0.0, 0.0}, wz[2] = {0.0, 0.0};
           double wx2[2] = {0.0, 0.0}, wy2[2] = {0.0, 0.0}, wz2[2] = {0.0, 0.0};
           if constexpr (R8)
           {
             const double xa0 = E1[8 * S + cp], xa1 = E1[8 * S + cp + 1];
             const double xd0 = E2[8 * S + cp], xd1 = E2[8 * S + cp + 1];
+            const double xz0 = FULL ? E4[8 * S + cp] : xa0, xz1 = FULL ? E4[8 * S + cp + 1] : xa1;
             wx[0] = FD[0].m8 * xa0, wx[1] = FD[0].m8 * xa1;
-            wz[0] = FA[0].m8 * xa0, wz[1] = FA[0].m8 * xa1;
+            wz[0] = FA[0].m8 * xz0, wz[1] = FA[0].m8 * xz1;
             wy[0] = FA[0].m8 * xd0, wy[1] = FA[0].m8 * xd1;
             wx2[0] = FD2.m8 * xa0, wx2[1] = FD2.m8 * xa1;
-            wz2[0] = FA2.m8 * xa0, wz2[1] = FA2.m8 * xa1;
+            wz2[0] = FA2.m8 * xz0, wz2[1] = FA2.m8 * xz1;
             wy2[0] = FA2.m8 * xd0, wy2[1] = FA2.m8 * xd1;
           }
           dmma(wx, FD[0].a0, ba0);  dmma(wx, FD[0].a1, ba1);   // Wx = (D x A x A) u   stiffness.hpp:68-70
-          dmma(wz, FA[0].a0, ba0);  dmma(wz, FA[0].a1, ba1);   // Wz = (A x A x A) u   :76-77 (REF_EXACT)
+          dmma(wz, FA[0].a0, bz0);  dmma(wz, FA[0].a1, bz1);   // Wz = (A x A x A) u   :76-77 (REF_EXACT) / (A x A x D) u (FULL)
           dmma(wy, FA[0].a0, bd0);  dmma(wy, FA[0].a1, bd1);   // Wy = (A x D x A) u   :72-74
           if constexpr (R8)
           {
             dmma(wx2, FD2.a0, ba0);  dmma(wx2, FD2.a1, ba1);
-            dmma(wz2, FA2.a0, ba0);  dmma(wz2, FA2.a1, ba1);
+            dmma(wz2, FA2.a0, bz0);  dmma(wz2, FA2.a1, bz1);
             dmma(wy2, FA2.a0, bd0);  dmma(wy2, FA2.a1, bd1);
           }
           // geometry (stiffness.hpp:14-29); only f2 is observable in REF_EXACT
@@ -472,37 +561,38 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
             sl = gRing + slot * PL::g_slot_bytes;
             pitch = PL::g_plane_pitch;
           }
-          if (N1 >= 8 || g < N1)
+          // records of the points (plane, cp) and (plane, cp + 1): [zz, yz, xz, yy, xy, xx] each
+          auto transform = [&](int plane, const double (&vx)[2], const double (&vy)[2], const double (&vz)[2])
           {
-            const double* r = reinterpret_cast<const double*>(sl + g * pitch) + 12 * t;
-            const double2 p0 = *reinterpret_cast<const double2*>(r);
-            const double2 p1 = *reinterpret_cast<const double2*>(r + 2);
+            const double* r = reinterpret_cast<const double*>(sl + plane * pitch) + 12 * t;
+            const double2 p0 = *reinterpret_cast<const double2*>(r);      // zz yz
+            const double2 p1 = *reinterpret_cast<const double2*>(r + 2);  // xz yy
             const double2 p3 = *reinterpret_cast<const double2*>(r + 6);
             const double2 p4 = *reinterpret_cast<const double2*>(r + 8);
-            const double f0 = fma(p0.x, wz[0], fma(p0.y, wy[0], p1.x * wx[0]));
-            const double f1 = fma(p3.x, wz[1], fma(p3.y, wy[1], p4.x * wx[1]));
-            if ((c0 & 1) == 0)
-              *reinterpret_cast<double2*>(E0 + g * S + cp) = make_double2(f0, f1);
-            else
-              E0[g * S + cp] = f0, E0[g * S + cp + 1] = f1; // the overlapping last tile starts on an odd column
-          }
-          if constexpr (R8)
-          {
-            if (g == 0)
+            const double f20 = fma(p0.x, vz[0], fma(p0.y, vy[0], p1.x * vx[0]));
+            const double f21 = fma(p3.x, vz[1], fma(p3.y, vy[1], p4.x * vx[1]));
+            auto put = [&](double* E, double a, double b)
             {
-              const double* r = reinterpret_cast<const double*>(sl + 8 * pitch) + 12 * t;
-              const double2 p0 = *reinterpret_cast<const double2*>(r);
-              const double2 p1 = *reinterpret_cast<const double2*>(r + 2);
-              const double2 p3 = *reinterpret_cast<const double2*>(r + 6);
-              const double2 p4 = *reinterpret_cast<const double2*>(r + 8);
-              const double f0 = fma(p0.x, wz2[0], fma(p0.y, wy2[0], p1.x * wx2[0]));
-              const double f1 = fma(p3.x, wz2[1], fma(p3.y, wy2[1], p4.x * wx2[1]));
               if ((c0 & 1) == 0)
-                *reinterpret_cast<double2*>(E0 + 8 * S + cp) = make_double2(f0, f1);
+                *reinterpret_cast<double2*>(E + plane * S + cp) = make_double2(a, b);
               else
-                E0[8 * S + cp] = f0, E0[8 * S + cp + 1] = f1;
+                E[plane * S + cp] = a, E[plane * S + cp + 1] = b; // the overlapping last tile starts on an odd column
+            };
+            put(E0, f20, f21);
+            if constexpr (FULL)
+            {
+              const double2 p2 = *reinterpret_cast<const double2*>(r + 4);  // xy xx
+              const double2 p5 = *reinterpret_cast<const double2*>(r + 10);
+              // f0 = xx wx + xy wy + xz wz,  f1 = xy wx + yy wy + yz wz   (tiled_kernels.cu, same expression order)
+              put(E3, fma(p1.x, vz[0], fma(p2.x, vy[0], p2.y * vx[0])), fma(p4.x, vz[1], fma(p5.x, vy[1], p5.y * vx[1])));
+              put(E5, fma(p0.y, vz[0], fma(p1.y, vy[0], p2.x * vx[0])), fma(p3.y, vz[1], fma(p4.y, vy[1], p5.x * vx[1])));
             }
-          }
+          };
+          if (N1 >= 8 || g < N1)
+            transform(g, wx, wy, wz);
+          if constexpr (R8)
+            if (g == 0)
+              transform(8, wx2, wy2, wz2);
           if constexpr (!PL::GB)
           {
             __syncwarp(); // every lane is done with this slot before the next tile's request overwrites it
@@ -515,7 +605,7 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
     if constexpr (OP == TC_MASS)
       if (cn < ncells)
         load_cell(Gm, jS, barJ, cn);
-    if constexpr (OP == TC_STIFF && PL::GB)
+    if constexpr (STIFF && PL::GB)
     {
       // every geometry value of this stage went into an E0 store before the barrier above (tma.cuh, rule 1): refill
       if (cell + PL::GST * stride < ncells)
@@ -526,7 +616,45 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
 
     // ---- backward: axis 0, axis 1, axis 2 ----------------------------------------------------------------------------------
     double* wS; // W staging, natural order (+ skew)
-    if constexpr (OP == TC_STIFF)
+    if constexpr (FULL)
+    {
+      // W = (D x A x A) f0 + (A x D x A) f1 + (A x A x D) f2, partial products merged as soon as they share the rest of
+      // their path:  axis 0: X = D0 f0, Y = A0 f1, Z = A0 f2 | axis 1: X' = A1 X + D1 Y, Z' = A1 Z | axis 2: A2 X' + D2 Z'
+      auto to_b = [&](double* E)
+      {
+        return [E](int, int i, int col, double v)
+        {
+          const int a1 = col / N1, a2 = col - a1 * N1;
+          E[a1 * S + i * N1 + a2] = v; // [a1][j0, a2]
+        };
+      };
+      tc_phase<N1, NW, 1>(E3, FD, tabD, [](int p, int col) { return p * S + col; }, to_b(E1), g, t, warp, tid);
+      tc_phase<N1, NW, 1>(E5, FA, tabA, [](int p, int col) { return p * S + col; }, to_b(E2), g, t, warp, tid);
+      tc_phase<N1, NW, 1>(E0, FA, tabA, [](int p, int col) { return p * S + col; }, to_b(E4), g, t, warp, tid);
+      block_sync();
+      tc_phase_sum<N1, NW>(
+          E1, E2, FA[0], FD[0], B.a, B.d, [](int p, int col) { return p * S + col; },
+          [&](int i, int col, double v)
+          {
+            const int j0 = col / N1, a2 = col - j0 * N1;
+            E0[a2 * S + j0 * N1 + i] = v; // [a2][j0, j1]
+          },
+          g, t, warp, tid);
+      tc_phase<N1, NW, 1>(
+          E4, FA, tabA, [](int p, int col) { return p * S + col; },
+          [&](int, int i, int col, double v)
+          {
+            const int j0 = col / N1, a2 = col - j0 * N1;
+            E3[a2 * S + j0 * N1 + i] = v;
+          },
+          g, t, warp, tid);
+      block_sync();
+      wS = E1;
+      tc_phase_sum<N1, NW>(
+          E0, E3, FA[0], FD[0], B.a, B.d, [](int p, int col) { return p * S + col; },
+          [&](int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
+    }
+    else if constexpr (STIFF)
     {
       // only W = (A x A x D) f2 is observable (stiffness.hpp:95-97 overwrites :83-91)
       tc_phase<N1, NW, 1>(
@@ -664,7 +792,27 @@ long long run_tc_n1(int n1, const double* A, const double* D, const double* U, d
                     size_t num_cells, cudaStream_t stream)
 {
   const long long v = opt_variant();
-  if constexpr (OP == TC_MASS)
+  if constexpr (OP == TC_STIFF_FULL)
+  {
+    // whole-cell geometry stages only; variant 31 / 33: the other stage count / more warps per cell
+    switch (n1)
+    {
+    case 6: return v == 31 ? run_tc<6, OP, 101, 5>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<6, OP, 102, 2>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<6, OP, 102, 5>(A, D, U, W, geom, num_cells, stream);
+    case 7: return v == 31 ? run_tc<7, OP, 101, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<7, OP, 102, 7>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<7, OP, 102, 4>(A, D, U, W, geom, num_cells, stream);
+    case 8: return v == 31 ? run_tc<8, OP, 102, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<8, OP, 101, 8>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<8, OP, 101, 4>(A, D, U, W, geom, num_cells, stream);
+    case 9: return v == 31 ? run_tc<9, OP, 102, 4>(A, D, U, W, geom, num_cells, stream)
+                 : v == 33 ? run_tc<9, OP, 101, 4>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<9, OP, 101, 6>(A, D, U, W, geom, num_cells, stream);
+    default: return 0;
+    }
+  }
+  else if constexpr (OP == TC_MASS)
   {
     switch (n1)
     {
@@ -734,8 +882,16 @@ long long launch_stiffness_tc(const StiffnessArgs<T>& a)
   {
     const int n1 = a.degree + 1;
     const long long tc = opt_tc();
-    if (tc == 0 || n1 < 6 || n1 > 9 || a.mode != FEMTC_STIFFNESS_REF_EXACT)
+    if (tc == 0 || n1 < 6 || n1 > 9)
       return 0;
+    if (a.mode == FEMTC_STIFFNESS_FULL)
+    {
+      // measured (profiles/r02_ab_tc_full.txt; % of measured HBM, column kernel -> DMMA): n1 = 6  57 -> 52 (stays on the
+      // column kernel), n1 = 7  45 -> 59, n1 = 8  51 -> 73, n1 = 9  37 -> 41
+      if (tc < 0 && n1 < 7)
+        return 0;
+      return run_tc_n1<TC_STIFF_FULL>(n1, a.A_host, a.D_host, a.U, a.W, a.G, a.num_cells, a.stream);
+    }
     if (tc < 0 && n1 < 7) // measured: n1 = 7, 8, 9 gain 12 / 20 / 4 points over the column kernel, n1 = 6 loses one
       return 0;
     return run_tc_n1<TC_STIFF>(n1, a.A_host, a.D_host, a.U, a.W, a.G, a.num_cells, a.stream);
