@@ -62,6 +62,7 @@ LaunchRecord& launch_record() { return t_record; }
 // ---- options ---------------------------------------------------------------------------------
 static std::atomic<long long> g_opt_kernel{0};
 static std::atomic<long long> g_opt_host_chunk_mb{64};
+static long long env_int(const char* name, long long lo, long long hi, long long dflt);
 static std::atomic<long long> g_opt_variant{0};
 static long long env_flag(const char* name)
 {
@@ -69,7 +70,6 @@ static long long env_flag(const char* name)
   return v && *v && *v != '0' ? 1 : 0;
 }
 static std::atomic<long long> g_opt_host_register{env_flag("FEMTC_HOST_REGISTER")};
-static std::atomic<long long> g_opt_tc{-1};
 static long long env_int(const char* name, long long lo, long long hi, long long dflt)
 {
   const char* v = std::getenv(name);
@@ -79,6 +79,7 @@ static long long env_int(const char* name, long long lo, long long hi, long long
   return x < lo || x > hi ? dflt : x;
 }
 static std::atomic<long long> g_opt_host_devices{env_int("FEMTC_HOST_DEVICES", 1, 64, 1)};
+static std::atomic<long long> g_opt_tc{env_int("FEMTC_TC", -1, 1, -1)}; // env: initial value of option "tc" (A/B runs of whole programs)
 
 long long opt_variant() { return g_opt_variant.load(); }
 long long opt_tc() { return g_opt_tc.load(); }

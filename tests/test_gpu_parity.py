@@ -926,7 +926,10 @@ REPEAT_CASES = (
     + [("stiffness", 5, "float64", 0, 0), ("stiffness", 5, "float64", 1, 0), ("stiffness", 5, "float32", 1, 0),
        ("stiffness", 6, "float64", 1, 0), ("stiffness", 7, "float32", 1, 0), ("stiffness", 8, "float64", 1, 0),
        ("stiffness", 6, "float32", 0, 4), ("stiffness", 7, "float64", 0, 4), ("stiffness", 8, "float32", 0, 4),
-       ("stiffness", 8, "float64", 0, 0), ("stiffness", 6, "float32", 0, 0), ("stiffness", 8, "float32", 0, 0)])
+       ("stiffness", 8, "float64", 0, 0), ("stiffness", 6, "float32", 0, 0), ("stiffness", 8, "float32", 0, 0)]
+    # variant -1: tensor-core family on (tc = 1): the whole-cell geometry stages of the DMMA kernels (round 2), both modes
+    + [("stiffness", 5, "float64", 0, -1), ("stiffness", 6, "float64", 0, -1), ("stiffness", 7, "float64", 1, -1),
+       ("stiffness", 8, "float64", 1, -1), ("stiffness", 8, "float64", 0, -1)])
 
 
 @pytest.mark.parametrize("op,P,dt,mode,variant", REPEAT_CASES)
@@ -941,9 +944,11 @@ def test_repeated_launches_on_cache_resident_fields_are_bit_identical(femtc, ora
     phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=70 + P, centred=True)
     ref = oracle_run(oracle, op, phi, U, geom, P, mode)
     dU, dg = torch.from_numpy(U).cuda(), torch.from_numpy(geom).cuda()
-    femtc.set_option("variant", variant)
-    if variant == 4:
-        femtc.set_option("tc", 0)
+    femtc.set_option("variant", max(variant, 0))
+    if variant == -1:
+        femtc.set_option("tc", 1)
+    elif variant == 4 or (mode == 1 and dt == "float64" and P >= 6):
+        femtc.set_option("tc", 0)           # the column kernels' private rings (FULL fp64 defaults to the DMMA family since round 2)
     try:
         first, differing = None, 0
         for _ in range(1000):
