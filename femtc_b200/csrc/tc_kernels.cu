@@ -83,11 +83,28 @@ struct TcTab
   double d[N1 * N1];
 };
 
+// Which two contraction indices p the lane (g, t) feeds to the two DMMAs of a tile.  Any split of 0..7 into two sets
+// of four works as long as table and data fragments agree.  Round 1 used {t, 4 + t}; with {2t, 2t + 1} (TC_KPERM) the
+// data a lane loads and the results it stores are both two NEIGHBOURING planes per t, so one plane stride serves both:
+// 64-bit shared-memory accesses are served per half-warp (g = 0..3 / 4..7 x t = 0..3), conflict-free when the word
+// stride between consecutive t is 8 or 24 mod 32 -- for loads AND stores that is 2 planes, i.e. S = 2 or 6 mod 8.
+// (Round 1: loads 1 plane apart, stores 2 planes apart, S = 4 mod 8: stores two-way conflicted; ncu, n1 = 8 mass kernel:
+// l1tex 94 %, 42 % of the shared-memory wavefronts excessive, profiles/r02_ncu_tc_mass_n1_8_before.txt.)
+#ifndef TC_KPERM
+#define TC_KPERM 1
+#endif
+__host__ __device__ constexpr int tc_k0(int t) { return TC_KPERM ? 2 * t : t; }
+__host__ __device__ constexpr int tc_k1(int t) { return TC_KPERM ? 2 * t + 1 : 4 + t; }
+
 constexpr int tc_plane_stride(int n2)
 {
   int s = n2;
-  while (s % 16 != 4 && s % 16 != 12)
-    ++s;
+  if (TC_KPERM)
+    while (s % 8 != 2 && s % 8 != 6)
+      ++s;
+  else
+    while (s % 16 != 4 && s % 16 != 12)
+      ++s;
   return s;
 }
 
@@ -140,8 +157,8 @@ template <int N1>
 __device__ __forceinline__ MFrag make_frag(const double* tab, int row, int t, bool valid)
 {
   MFrag f;
-  f.a0 = (valid && row < N1 && t < N1) ? tab[row + t * N1] : 0.0;
-  f.a1 = (valid && row < N1 && 4 + t < N1) ? tab[row + (4 + t) * N1] : 0.0;
+  f.a0 = (valid && row < N1 && tc_k0(t) < N1) ? tab[row + tc_k0(t) * N1] : 0.0;
+  f.a1 = (valid && row < N1 && tc_k1(t) < N1) ? tab[row + tc_k1(t) * N1] : 0.0;
   f.m8 = (valid && N1 == 9 && row < N1) ? tab[row + 8 * N1] : 0.0;
   return f;
 }
@@ -162,7 +179,7 @@ __device__ __forceinline__ void tc_phase(const double* in, const MFrag (&M)[NM],
     if ((k + 1) * NW > NT && tile >= NT)
       break;
     const int c0 = (8 * tile + 8 <= N2) ? 8 * tile : N2 - 8;
-    const double b0 = in[ain(t, c0 + g)], b1 = in[ain(4 + t, c0 + g)];
+    const double b0 = in[ain(tc_k0(t), c0 + g)], b1 = in[ain(tc_k1(t), c0 + g)];
     double acc[NM][2];
     if constexpr (R8)
     {
@@ -237,8 +254,8 @@ __device__ __forceinline__ void tc_phase_sum(const double* in0, const double* in
     if ((k + 1) * NW > NT && tile >= NT)
       break;
     const int c0 = (8 * tile + 8 <= N2) ? 8 * tile : N2 - 8;
-    const double x0 = in0[ain(t, c0 + g)], x1 = in0[ain(4 + t, c0 + g)];
-    const double y0 = in1[ain(t, c0 + g)], y1 = in1[ain(4 + t, c0 + g)];
+    const double x0 = in0[ain(tc_k0(t), c0 + g)], x1 = in0[ain(tc_k1(t), c0 + g)];
+    const double y0 = in1[ain(tc_k0(t), c0 + g)], y1 = in1[ain(tc_k1(t), c0 + g)];
     double acc[2] = {0.0, 0.0};
     if constexpr (R8)
     {
@@ -490,7 +507,7 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
         const int cp = c0 + 2 * t;
         if constexpr (OP == TC_MASS)
         {
-          const double b0 = E1[t * S + c0 + g], b1 = E1[(4 + t) * S + c0 + g];
+          const double b0 = E1[tc_k0(t) * S + c0 + g], b1 = E1[tc_k1(t) * S + c0 + g];
           double v[2] = {0.0, 0.0}, v2[2] = {0.0, 0.0};
           if constexpr (R8)
           {
@@ -518,10 +535,10 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
         }
         else
         {
-          const double ba0 = E1[t * S + c0 + g], ba1 = E1[(4 + t) * S + c0 + g];
-          const double bd0 = E2[t * S + c0 + g], bd1 = E2[(4 + t) * S + c0 + g];
+          const double ba0 = E1[tc_k0(t) * S + c0 + g], ba1 = E1[tc_k1(t) * S + c0 + g];
+          const double bd0 = E2[tc_k0(t) * S + c0 + g], bd1 = E2[tc_k1(t) * S + c0 + g];
           // the z term: REF_EXACT uses A0 A1 A2 u (stiffness.hpp:76-77 as coded), FULL the real A0 A1 D2 u
-          const double bz0 = FULL ? E4[t * S + c0 + g] : ba0, bz1 = FULL ? E4[(4 + t) * S + c0 + g] : ba1;
+          const double bz0 = FULL ? E4[tc_k0(t) * S + c0 + g] : ba0, bz1 = FULL ? E4[tc_k1(t) * S + c0 + g] : ba1;
           double wx[2] = {0.0, 0.0}, wy[2] = {0.0, 0.0}, wz[2] = {0.0, 0.0};
           double wx2[2] = {0.0, 0.0}, wy2[2] = {0.0, 0.0}, wz2[2] = {0.0, 0.0};
           if constexpr (R8)
