@@ -238,6 +238,37 @@ __device__ __forceinline__ void tc_phase(const double* in, const MFrag (&M)[NM],
   }
 }
 
+// Last contraction of a cell, even n1: the two DMMA operands change places, so lane (g, t) ends up with
+// Y[i = 2t, 2t + 1][col = c0 + g] -- two neighbouring values of the natural W layout, stored by ONE 128-bit store whose
+// quarter-warps (g = 2q, 2q + 1; t = 0..3) cover all 32 banks.  The round-1 form (lane holds two columns of one i)
+// stored 64-bit values 16 doubles apart: four-way conflicts, 96 of the 160 excessive wavefronts per cell of the n1 = 8
+// mass kernel (profiles/r02_ncu_tc_mass_n1_8.txt).  TWO: Y = M0 . X0 + M1 . X1 (FULL).
+template <int N1, int NW, bool TWO, class AIN>
+__device__ __forceinline__ void tc_phase_w(const double* in0, const double* in1, const MFrag& M0, const MFrag& M1, double* w,
+                                           AIN ain, int g, int t, int warp)
+{
+  static_assert(N1 % 2 == 0, "natural rows of an odd n1 are not 16-byte aligned");
+  constexpr int N2 = N1 * N1, NT = (N2 + 7) / 8;
+#pragma unroll
+  for (int k = 0; k < (NT + NW - 1) / NW; ++k)
+  {
+    const int tile = warp + k * NW;
+    if ((k + 1) * NW > NT && tile >= NT)
+      break;
+    const int c0 = (8 * tile + 8 <= N2) ? 8 * tile : N2 - 8;
+    double acc[2] = {0.0, 0.0};
+    dmma(acc, in0[ain(tc_k0(t), c0 + g)], M0.a0);
+    dmma(acc, in0[ain(tc_k1(t), c0 + g)], M0.a1);
+    if constexpr (TWO)
+    {
+      dmma(acc, in1[ain(tc_k0(t), c0 + g)], M1.a0);
+      dmma(acc, in1[ain(tc_k1(t), c0 + g)], M1.a1);
+    }
+    if (N1 >= 8 || 2 * t < N1)
+      *reinterpret_cast<double2*>(w + (c0 + g) * N1 + 2 * t) = make_double2(acc[0], acc[1]);
+  }
+}
+
 // Y = M0 . X0 + M1 . X1: two inputs in the same layout accumulated into one output (the backward sweeps of the
 // FULL operator, where two partial products meet before the next axis).
 template <int N1, int NW, class AIN, class SOUT>
@@ -667,9 +698,12 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
           g, t, warp, tid);
       block_sync();
       wS = E1;
-      tc_phase_sum<N1, NW>(
-          E0, E3, FA[0], FD[0], B.a, B.d, [](int p, int col) { return p * S + col; },
-          [&](int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
+      if constexpr (N1 % 2 == 0)
+        tc_phase_w<N1, NW, true>(E0, E3, FA[0], FD[0], wS, [](int p, int col) { return p * S + col; }, g, t, warp);
+      else
+        tc_phase_sum<N1, NW>(
+            E0, E3, FA[0], FD[0], B.a, B.d, [](int p, int col) { return p * S + col; },
+            [&](int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
     }
     else if constexpr (STIFF)
     {
@@ -693,9 +727,12 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
           g, t, warp, tid);
       block_sync();
       wS = E1;
-      tc_phase<N1, NW, 1>(
-          E2, FD, tabD, [](int p, int col) { return p * S + col; },
-          [&](int, int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
+      if constexpr (N1 % 2 == 0)
+        tc_phase_w<N1, NW, false>(E2, E2, FD[0], FD[0], wS, [](int p, int col) { return p * S + col; }, g, t, warp);
+      else
+        tc_phase<N1, NW, 1>(
+            E2, FD, tabD, [](int p, int col) { return p * S + col; },
+            [&](int, int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
     }
     else
     {
@@ -718,9 +755,12 @@ tc_kernel(const __grid_constant__ TcTab<N1> B, const double* __restrict__ U, dou
           g, t, warp, tid);
       block_sync();
       wS = E2;
-      tc_phase<N1, NW, 1>(
-          E1, FA, tabA, [](int p, int col) { return p * S + col; },
-          [&](int, int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
+      if constexpr (N1 % 2 == 0)
+        tc_phase_w<N1, NW, false>(E1, E1, FA[0], FA[0], wS, [](int p, int col) { return p * S + col; }, g, t, warp);
+      else
+        tc_phase<N1, NW, 1>(
+            E1, FA, tabA, [](int p, int col) { return p * S + col; },
+            [&](int, int i, int col, double v) { wS[sk + col * N1 + i] = v; }, g, t, warp, tid);
     }
     fence_proxy_async();
     block_sync();
