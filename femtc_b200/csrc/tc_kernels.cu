@@ -886,8 +886,8 @@ long long run_tc_n1(int n1, const double* A, const double* D, const double* U, d
     switch (n1)
     {
     case 6: return v == 31 ? run_tc<6, OP, 102, 2>(A, D, U, W, geom, num_cells, stream)
-                 : v == 33 ? run_tc<6, OP, 102, 5>(A, D, U, W, geom, num_cells, stream)
-                           : run_tc<6, OP, 3, 2>(A, D, U, W, geom, num_cells, stream);
+                 : v == 30 ? run_tc<6, OP, 3, 2>(A, D, U, W, geom, num_cells, stream)
+                           : run_tc<6, OP, 102, 5>(A, D, U, W, geom, num_cells, stream);
     // Geometry transport (profiles/r02_ab_tc_geometry_stages.txt; % of measured HBM, burst): whole-cell stages filled by
     // bulk copies replace the per-warp cp.async rings of round 1 (variant 30):  n1 = 7  74.5 -> 87.2 (2 stages; 3: 81.0),
     // n1 = 8  92.4 -> 102.2 (2),  n1 = 9  67.2 -> 74.2 (1 stage; 2 stages cost a resident block: 66.4).
@@ -949,8 +949,8 @@ long long launch_stiffness_tc(const StiffnessArgs<T>& a)
         return 0;
       return run_tc_n1<TC_STIFF_FULL>(n1, a.A_host, a.D_host, a.U, a.W, a.G, a.num_cells, a.stream);
     }
-    if (tc < 0 && n1 < 7) // measured: n1 = 7, 8, 9 gain 12 / 20 / 4 points over the column kernel, n1 = 6 loses one
-      return 0;
+    // measured against the column kernels (% of measured HBM, burst): n1 = 6  88 -> 92 (whole-cell stages, 5 warps per
+    // cell), n1 = 7  69 -> 94, n1 = 8  73 -> 107, n1 = 9  68 -> 79: the family serves every REF_EXACT shape it covers
     return run_tc_n1<TC_STIFF>(n1, a.A_host, a.D_host, a.U, a.W, a.G, a.num_cells, a.stream);
   }
   return 0;
