@@ -947,8 +947,8 @@ def test_repeated_launches_on_cache_resident_fields_are_bit_identical(femtc, ora
     femtc.set_option("variant", max(variant, 0))
     if variant == -1:
         femtc.set_option("tc", 1)
-    elif variant == 4 or (mode == 1 and dt == "float64" and P >= 6):
-        femtc.set_option("tc", 0)           # the column kernels' private rings (FULL fp64 defaults to the DMMA family since round 2)
+    elif variant == 4 or (op == "stiffness" and dt == "float64" and P >= 5):
+        femtc.set_option("tc", 0)           # the column kernels' rings (fp64 stiffness at P >= 5 defaults to the DMMA family since round 2)
     try:
         first, differing = None, 0
         for _ in range(1000):
