@@ -22,37 +22,76 @@ namespace
 
 constexpr int kThreads = 256;
 
-// Y[c][j*n1 + i] = sum_p M[i + p*n1] * X[c][p*n2 + j]   for a group of `cells` cells.
+// Y[c][j*n1 + i] = sum_p M(i,p) * X[c][p*n2 + j]   for a group of `cells` cells.
 // Optional fused epilogues:  * scale[c][idx]   or   (add0 + add1) + result.
+// A thread owns IB = 4 consecutive outputs i of one column j: per p it loads X once and the four table entries as one
+// or two 128-bit words (the table is staged with rows padded to a multiple of 4, M(i,p) = Mp[p * n1p + i]), i.e.
+// 2-3 shared-memory loads per 4 FMAs instead of the 8 of the one-output-per-thread form (round 1) -- the sweep of
+// degrees 9..25 and of every ragged tail.  p ascends exactly as before: results are bit-identical to round 1.
+constexpr int kIB = 4;
+__host__ __device__ constexpr int pad4(int n) { return (n + kIB - 1) / kIB * kIB; }
+
 template <typename T>
-__device__ __forceinline__ void sweep(const T* __restrict__ M, const T* X, size_t xstride, T* Y,
+__device__ __forceinline__ void sweep(const T* __restrict__ Mp, const T* X, size_t xstride, T* Y,
                                       size_t ystride, int n1, int cells, const T* scale = nullptr,
                                       size_t sstride = 0, const T* add0 = nullptr,
                                       const T* add1 = nullptr, size_t astride = 0)
 {
-  const int n2 = n1 * n1, nd = n2 * n1;
-  for (int t = threadIdx.x; t < cells * nd; t += blockDim.x)
+  const int n2 = n1 * n1, nd = n2 * n1, n1p = pad4(n1), nib = n1p / kIB;
+  const int per_cell = n2 * nib;
+  for (int t = threadIdx.x; t < cells * per_cell; t += blockDim.x)
   {
-    const int c = t / nd, idx = t - c * nd;
-    const int j = idx / n1, i = idx - j * n1;
+    const int c = t / per_cell, r = t - c * per_cell;
+    const int j = r / nib, i0 = (r - j * nib) * kIB;
     const T* x = X + (size_t)c * xstride + j;
-    T acc = T(0);
+    const T* m = Mp + i0;
+    T acc[kIB] = {T(0), T(0), T(0), T(0)};
     for (int p = 0; p < n1; ++p)
-      acc = fma_t(M[i + p * n1], x[(size_t)p * n2], acc);
-    if (scale)
-      acc = acc * scale[(size_t)c * sstride + idx];
-    if (add0)
-      acc = (add0[(size_t)c * astride + idx] + add1[(size_t)c * astride + idx]) + acc;
-    Y[(size_t)c * ystride + idx] = acc;
+    {
+      const T xv = x[(size_t)p * n2];
+      T mv[kIB];
+      if constexpr (sizeof(T) == 4)
+      {
+        const float4 q = *reinterpret_cast<const float4*>(m + p * n1p);
+        mv[0] = q.x, mv[1] = q.y, mv[2] = q.z, mv[3] = q.w;
+      }
+      else
+      {
+        const double2 q0 = *reinterpret_cast<const double2*>(m + p * n1p);
+        const double2 q1 = *reinterpret_cast<const double2*>(m + p * n1p + 2);
+        mv[0] = q0.x, mv[1] = q0.y, mv[2] = q1.x, mv[3] = q1.y;
+      }
+#pragma unroll
+      for (int k = 0; k < kIB; ++k)
+        acc[k] = fma_t(mv[k], xv, acc[k]);
+    }
+    const int base = j * n1 + i0;
+#pragma unroll
+    for (int k = 0; k < kIB; ++k)
+      if (i0 + k < n1)
+      {
+        T v = acc[k];
+        const int idx = base + k;
+        if (scale)
+          v = v * scale[(size_t)c * sstride + idx];
+        if (add0)
+          v = (add0[(size_t)c * astride + idx] + add1[(size_t)c * astride + idx]) + v;
+        Y[(size_t)c * ystride + idx] = v;
+      }
   }
   __syncthreads();
 }
 
+// table staging: M(i,p) = src[i + p*n1] -> dst[p*n1p + i], rows zero-padded to n1p = pad4(n1)
 template <typename T>
-__device__ __forceinline__ void load_matrix(T* dst, const T* __restrict__ src, int n)
+__device__ __forceinline__ void load_matrix(T* dst, const T* __restrict__ src, int n1)
 {
-  for (int t = threadIdx.x; t < n; t += blockDim.x)
-    dst[t] = src[t];
+  const int n1p = pad4(n1);
+  for (int t = threadIdx.x; t < n1 * n1p; t += blockDim.x)
+  {
+    const int p = t / n1p, i = t - p * n1p;
+    dst[t] = i < n1 ? src[i + p * n1] : T(0);
+  }
 }
 
 // The 1-D tables of the tuned degrees (n1 <= 9) travel as kernel parameters like in every other family: the ragged tail
@@ -65,10 +104,14 @@ struct SmallTab
   T a[kSmallN1 * kSmallN1], d[kSmallN1 * kSmallN1];
 };
 template <typename T>
-__device__ __forceinline__ void load_matrix_param(T* dst, const T* src, int n)
+__device__ __forceinline__ void load_matrix_param(T* dst, const T* src, int n1)
 {
-  for (int t = threadIdx.x; t < n; t += blockDim.x)
-    dst[t] = src[t];
+  const int n1p = pad4(n1);
+  for (int t = threadIdx.x; t < n1 * n1p; t += blockDim.x)
+  {
+    const int p = t / n1p, i = t - p * n1p;
+    dst[t] = i < n1 ? src[i + p * n1] : T(0);
+  }
 }
 
 // mass.hpp:10-49.  Scratch: 2 buffers of cpb*nd values, in shared memory when `ws` is null,
@@ -82,12 +125,13 @@ mass_generic_kernel(const T* __restrict__ phi, const __grid_constant__ SmallTab<
   T* A = reinterpret_cast<T*>(smem_raw);
   const int n2 = n1 * n1;
   const size_t nd = (size_t)n2 * n1;
-  T* b0 = ws ? ws + (size_t)blockIdx.x * 2 * cpb * nd : A + n2;
+  const int nt = n1 * pad4(n1); // staged table: rows padded to a multiple of 4 (16-byte aligned rows)
+  T* b0 = ws ? ws + (size_t)blockIdx.x * 2 * cpb * nd : A + nt;
   T* b1 = b0 + (size_t)cpb * nd;
   if (phi)
-    load_matrix(A, phi, n2);
+    load_matrix(A, phi, n1);
   else
-    load_matrix_param(A, tab.a, n2);
+    load_matrix_param(A, tab.a, n1);
   __syncthreads();
 
   const size_t groups = (num_cells + cpb - 1) / cpb;
@@ -115,23 +159,24 @@ stiffness_generic_kernel(const T* __restrict__ phiA, const T* __restrict__ phiD,
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* A = reinterpret_cast<T*>(smem_raw);
   const int n2 = n1 * n1;
-  T* D = A + n2;
+  const int nt = n1 * pad4(n1);
+  T* D = A + nt;
   const size_t nd = (size_t)n2 * n1;
   const size_t bs = (size_t)cpb * nd;
-  T* t0 = ws ? ws + (size_t)blockIdx.x * 5 * bs : D + n2;
+  T* t0 = ws ? ws + (size_t)blockIdx.x * 5 * bs : D + nt;
   T* t1 = t0 + bs;
   T* wx = t1 + bs;
   T* wy = wx + bs;
   T* wz = wy + bs;
   if (phiA)
   {
-    load_matrix(A, phiA, n2);
-    load_matrix(D, phiD, n2);
+    load_matrix(A, phiA, n1);
+    load_matrix(D, phiD, n1);
   }
   else
   {
-    load_matrix_param(A, tab.a, n2);
-    load_matrix_param(D, tab.d, n2);
+    load_matrix_param(A, tab.a, n1);
+    load_matrix_param(D, tab.d, n1);
   }
   __syncthreads();
 
@@ -414,14 +459,15 @@ int launch_mass_generic(const MassArgs<T>& a)
   const int n1 = a.degree + 1, n2 = n1 * n1;
   const size_t nd = (size_t)n2 * n1;
   int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
-  size_t smem = (n2 + 2 * cpb * nd) * sizeof(T);
+  const size_t nt = (size_t)n1 * pad4(n1);
+  size_t smem = (nt + 2 * cpb * nd) * sizeof(T);
   const size_t groups = (a.num_cells + cpb - 1) / cpb;
   int grid = (int)min(groups, (size_t)sm_count() * 8);
   const bool spill = smem > kGenericSmemMax; // the per-cell work arrays live in global scratch instead
   if (spill)
   {
     cpb = 1;
-    smem = n2 * sizeof(T);
+    smem = nt * sizeof(T);
     grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
   }
   note_launch(FAMILY_GENERIC, spill, mass_generic_kernel<T>, cpb, 0, grid, kThreads, smem);
@@ -457,14 +503,15 @@ int launch_stiffness_generic(const StiffnessArgs<T>& a)
   const int n1 = a.degree + 1, n2 = n1 * n1;
   const size_t nd = (size_t)n2 * n1;
   int cpb = (int)max((size_t)1, (size_t)kThreads / nd);
-  size_t smem = (2 * n2 + 5 * cpb * nd) * sizeof(T);
+  const size_t nt = (size_t)n1 * pad4(n1);
+  size_t smem = (2 * nt + 5 * cpb * nd) * sizeof(T);
   const size_t groups = (a.num_cells + cpb - 1) / cpb;
   int grid = (int)min(groups, (size_t)sm_count() * 8);
   const bool spill = smem > kGenericSmemMax;
   if (spill)
   {
     cpb = 1;
-    smem = 2 * n2 * sizeof(T);
+    smem = 2 * nt * sizeof(T);
     grid = (int)min(a.num_cells, (size_t)sm_count() * 4);
   }
   note_launch(FAMILY_GENERIC, spill, stiffness_generic_kernel<T>, cpb, 0, grid, kThreads, smem);
