@@ -149,6 +149,21 @@ def test_resident_operator_matches_drop_in_entry_points(femtc, oracle, torch_cud
         K.apply(U, np.empty_like(U))                       # destroyed by the context manager
 
 
+def test_resident_operator_left_to_the_interpreter_exit_is_silent():
+    """A handle that is never destroyed explicitly is released by __del__, also when that runs during interpreter
+    shutdown (module globals may already be gone): no traceback, exit code 0."""
+    import sys
+    code = (
+        "import numpy as np, femtc_b200 as f\n"
+        "phi = np.ones(32); g = np.ones(6 * 64 * 100); U = np.ones(64 * 100); W = np.zeros(64 * 100)\n"
+        "K = f.ResidentOperator('stiffness', phi, g, 100, 3)\n"
+        "assert K.apply(U, W) == 0 and W.min() > 0\n"
+        "keep = [K, f.ResidentOperator('mass', phi[:16], g[:6400], 100, 3)]\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=str(ROOT), timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Traceback" not in r.stderr and "Exception ignored" not in r.stderr, r.stderr
+
+
 def test_host_register_option_pins_caller_buffers_once(femtc, oracle):
     """Option "host_register": pageable caller buffers are page-locked in place on first sight and the
     registration is reused; results are unchanged; femtc_release_cache() drops the registrations."""
