@@ -322,7 +322,7 @@ def strong_leg(a, rank, local_rank, world, dev, *, op, degree, dtype, mode_name,
     with ClockSampler(local_rank) as clocks:
         ms, parts, worst = sweep(steps, True)
         # keep the same load up for a moment so that a short leg still collects clock samples
-        t_end = time.perf_counter() + 0.4
+        t_end = time.perf_counter() + 1.0
         while time.perf_counter() < t_end:
             apply(min(chunk, hi - lo))
             torch.cuda.synchronize()
