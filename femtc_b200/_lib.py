@@ -44,6 +44,7 @@ def _load() -> C.CDLL:
         getattr(lib, f"femtc_checksum_device_{s}").argtypes = [vp, sz, vp, vp]
         getattr(lib, f"femtc_fill_uniform_device_{s}").argtypes = [vp, sz, u64, u64, u64, i, vp]
         getattr(lib, f"femtc_operator_create_{s}").argtypes = [C.POINTER(vp), i, vp, sz, vp, sz, i, i]
+    lib.femtc_apply_contractions_device_static_f64.argtypes = [i] * 3 + [vp] * 5 + [sz, vp]
     lib.femtc_stream_probe_device.argtypes = [vp, vp, sz, i, vp]
     lib.femtc_operator_apply.argtypes = [vp, vp, vp]
     lib.femtc_operator_apply_device.argtypes = [vp, vp, vp, vp]

@@ -1121,6 +1121,24 @@ int femtc_apply_contractions_device_f32(int Na, int Nb, int Tr, const float* I0,
   return apply_contractions_device<float>(Na, Nb, Tr, I0, I1, I2, dB, dA, batch, (cudaStream_t)stream);
 }
 
+// The general contraction kernel with its scratch in the library's own __device__ array (generic_kernels.cu): for
+// callers that must not cause a device allocation.  Same argument checks as apply_contractions_device; shapes whose
+// scratch does not fit the array are refused (launch_apply_contractions_static words the message).
+int femtc_apply_contractions_device_static_f64(int Na, int Nb, int Tr, const double* I0, const double* I1,
+                                               const double* I2, const double* dB, double* dA, size_t batch,
+                                               void* stream)
+{
+  if (Na < 1 || Nb < 1 || Na > 64 || Nb > 64 || !I0 || !I1 || !I2 || (batch && (!dA || !dB)))
+  {
+    set_error("bad apply_contractions shape or null pointer");
+    return FEMTC_ERR_ARG;
+  }
+  int rc = require_device();
+  if (rc)
+    return rc;
+  return launch_apply_contractions_static(Na, Nb, Tr, I0, I1, I2, dB, dA, batch, (cudaStream_t)stream);
+}
+
 int femtc_string2order(const char* name)
 {
   static const char* names[6] = {"ijk", "ikj", "jik", "jki", "kij", "kji"};

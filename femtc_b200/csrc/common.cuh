@@ -140,6 +140,10 @@ int launch_fill_uniform(T* dX, size_t n, uint64_t seed, uint64_t stream_id, uint
 // tf32_kernels.cu -- tcgen05.mma kind::tf32 arm (fp32 mass n1 = 8), selected with option tc = 1; same convention
 long long launch_mass_tf32(const MassArgs<float>& a);
 int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, int reads, cudaStream_t s);
+// generic_kernels.cu -- the general contraction kernel with all of its scratch in a file-scope __device__ array (no
+// allocation on the call path); I0..I2 host pointers
+int launch_apply_contractions_static(int Na, int Nb, int Tr, const double* I0, const double* I1, const double* I2,
+                                     const double* dB, double* dA, size_t batch, cudaStream_t s);
 
 // tiled_kernels.cu -- degrees 1..8, TMA-staged warp tiles.  Return value:
 //   >= 0 : number of leading cells processed on the fast path (the caller runs the generic

@@ -686,8 +686,88 @@ int launch_stream_probe(const void* d_in, void* d_out, size_t bytes_per_stream, 
   return FEMTC_OK;
 }
 
+// ---- apply_contractions for callers that cannot allocate device memory -------------------------------------------
+// launch_apply_contractions above takes its three matrices and (for large shapes) its per-block work arrays from
+// cudaMallocAsync.  Some users of this library cannot afford that: a solver that handed the whole of HBM to its own arena
+// at start-up (an allocation made behind its back fails, or eats memory the arena has promised to someone else), and a
+// time-stepping loop that must not meet the device-wide synchronisation cudaMalloc / cudaFree may imply.  For them the
+// same kernel runs with every scratch byte in the array below: it belongs to the library image, so each GPU that loads
+// libfemtc_b200.so carries these 4 MiB from load to exit, and nothing is requested from the allocator per call.
+//
+// Layout of a call:  [ I0 | I1 | I2 ]  3*Na*Nb values, rounded up to 256 bytes, then one (Na*Nb*Nb + Na*Na*Nb)-value
+// work slice per block.  Every byte a call reads it has written itself (the matrices by the copies below, a work slice by
+// the sweep before the one that reads it), so whatever the previous call left behind is harmless and nothing has to be
+// cleared.  There is ONE array per device: two calls that run on the GPU at the same time (different streams, no
+// dependency) overwrite each other's matrices and work slices.
+constexpr size_t kStaticScratchBytes = size_t(4) << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// `g_static_scratch` in host code is only a handle for the runtime's symbol table, not an address the GPU understands;
+// the device address differs from device to device and is asked for once per device, with that device current.
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_addr[kStaticMaxDevices];
+
+static int static_scratch_address(unsigned char** out)
+{
+  int dev = 0;
+  FEMTC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices)
+  {
+    set_error("static scratch: device ordinal beyond 63");
+    return FEMTC_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev])
+  {
+    void* p = nullptr;
+    FEMTC_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_addr[dev];
+  return FEMTC_OK;
+}
+
+// I0..I2 host pointers, dB / dA device pointers.  No cudaMalloc*, cudaFree* or other allocating call on this path; the
+// first call on a device looks the array's address up (static_scratch_address).
+int launch_apply_contractions_static(int Na, int Nb, int Tr, const double* I0, const double* I1, const double* I2,
+                                     const double* dB, double* dA, size_t batch, cudaStream_t s)
+{
+  using T = double;
+  const size_t na = Na, nb = Nb, nm = na * nb;
+  const size_t tables = (3 * nm * sizeof(T) + 255) & ~size_t(255);
+  const size_t slice = (na * nb * nb + na * na * nb) * sizeof(T);
+  if (tables + slice > kStaticScratchBytes)
+  {
+    char msg[224];
+    std::snprintf(msg, sizeof msg,
+                  "apply_contractions (no-allocation entry): Na = %d, Nb = %d needs %zu bytes of scratch, the built-in "
+                  "array holds %zu; use femtc_apply_contractions_device_f64 for this shape",
+                  Na, Nb, tables + slice, kStaticScratchBytes);
+    set_error(msg);
+    return FEMTC_ERR_ARG;
+  }
+  if (batch == 0)
+    return FEMTC_OK;
+  unsigned char* base = nullptr;
+  int rc = static_scratch_address(&base);
+  if (rc)
+    return rc;
+  T* dI = reinterpret_cast<T*>(base);
+  T* ws = reinterpret_cast<T*>(base + tables);
+  const size_t fit = (kStaticScratchBytes - tables) / slice; // work slices the array has room for
+  const int grid = (int)min(min(batch, fit), (size_t)sm_count() * 8);
+  FEMTC_CUDA(cudaMemcpyAsync(dI, I0, nm * sizeof(T), cudaMemcpyHostToDevice, s));
+  FEMTC_CUDA(cudaMemcpyAsync(dI + nm, I1, nm * sizeof(T), cudaMemcpyHostToDevice, s));
+  FEMTC_CUDA(cudaMemcpyAsync(dI + 2 * nm, I2, nm * sizeof(T), cudaMemcpyHostToDevice, s));
+  apply_contractions_kernel<T><<<grid, kThreads, 0, s>>>(Na, Nb, Tr, dI, dI + nm, dI + 2 * nm, dB, dA, batch, ws);
+  count_launch();
+  FEMTC_CUDA(cudaGetLastError());
+  return FEMTC_OK;
+}
+
 #define INSTANTIATE(T)                                                                             \
-  template int launch_mass_generic<T>(const MassArgs<T>&);                                         \
+  template int launch_mass_generic<T>(const MassArgs<T>&);                                     \
   template int launch_stiffness_generic<T>(const StiffnessArgs<T>&);                               \
   template int launch_gemm_blocked<T>(int, int, int, const T*, const T*, T*, cudaStream_t);        \
   template int launch_gemm_strided<T>(int, int, int, int, int, int, int, int, const T*, const T*,  \

@@ -191,6 +191,33 @@ int femtc_apply_contractions_device_f32(int Na, int Nb, int Tr, const float* I0,
                                         const float* I2, const float* dB, float* dA, size_t batch,
                                         void* stream);
 
+/* No counterpart in the reference (its apply_contractions takes a caller-made Buffer on the CPU, tmm.hpp:46-60; the
+ * question of who allocates GPU scratch does not arise there).
+ *
+ * femtc_apply_contractions_device_f64 for callers that cannot let the library allocate device memory.  The general
+ * kernel behind that entry point asks the stream-ordered allocator for room for the three matrices and, for large
+ * shapes, for its work arrays.  That is unwelcome in two kinds of program that use this library: a solver that reserved
+ * all of HBM for its own memory arena when it started, where a hidden allocation either fails or takes memory the arena
+ * has already promised; and a time-stepping loop with a latency budget, which cannot risk the device-wide
+ * synchronisation an allocation or a free may bring.  This entry point calls no cudaMalloc / cudaFree of any flavour:
+ * its scratch is a 4 MiB (4 194 304 byte) array that is part of the library image, so every GPU that loads
+ * libfemtc_b200.so holds those 4 MiB until the process exits, used or not.
+ *
+ * Arguments, layouts and result as femtc_apply_contractions_device_f64 (I0, I1, I2 HOST pointers, dB / dA DEVICE
+ * pointers, asynchronous on `stream`), always on the general kernel (the tiled TMA kernel is not used here), so results
+ * agree with the other entry point to rounding.
+ * Limit: 8 * (3*Na*Nb rounded up to 32 values + Na*Nb*(Na+Nb)) bytes must fit in the array -- e.g. Na = Nb <= 63; a
+ * larger shape returns FEMTC_ERR_ARG, says so in femtc_last_error() and leaves dA untouched.  Large shapes run on
+ * fewer blocks (as many work slices as fit), i.e. slower than the allocating entry point.
+ * First call on each device: looks up the array's device address (once per device, remembered).  Make that first call
+ * ahead of any stream capture.
+ * Sharing: all calls on a device use the same array and it keeps what the last call wrote.  Nothing needs to start at
+ * zero (a call reads only what it wrote itself), but two calls that can run on the GPU at the same time -- different
+ * streams with no dependency between them -- corrupt each other: keep calls on one device stream-ordered. */
+int femtc_apply_contractions_device_static_f64(int Na, int Nb, int Tr, const double* I0, const double* I1,
+                                               const double* I2, const double* dB, double* dA, size_t batch,
+                                               void* stream);
+
 /* linalg::string2order (reference src/linalg.hpp:21-37): returns 0..5, or -1 where the
  * reference throws std::runtime_error("Invalid loop order"). */
 int femtc_string2order(const char* name);
