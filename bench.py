@@ -68,6 +68,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="skip the 48-entry degree sweep (N = 1 only)")
+    ap.add_argument("--detail-file", default="", help="where the full record behind the compact stdout line is written "
+                                                      "(default gpurun_out/bench_detail_n<N>.json)")
     ap.add_argument("--sweep-cells", type=int, default=1_000_000)
     ap.add_argument("--sweep-filter", default="", help="development: only entries whose name contains this")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (BASELINE config 5)")
@@ -523,6 +525,114 @@ def stream_peaks(dev):
     return out
 
 
+# ------------------------------------------------------------------------------------------------------
+# The ONE stdout line stays small at every N (round 2 lost its N = 1 line to a 52 KB print): the line carries a compact
+# form, the full record goes to a side file.
+# ------------------------------------------------------------------------------------------------------
+LINE_LIMIT = 6000  # bytes of the printed line, enforced by fit_line
+SWEEP_COLS = ["frac", "frac_min", "gdofs", "err_over_tol", "sm_mhz"]
+
+
+def sig(x, n=6):
+    """Floats rounded to n significant digits, recursively (ints, strings, None untouched)."""
+    if isinstance(x, float):
+        return float(f"{x:.{n}g}") if np.isfinite(x) else None
+    if isinstance(x, dict):
+        return {k: sig(v, n) for k, v in x.items()}
+    if isinstance(x, (list, tuple)):
+        return [sig(v, n) for v in x]
+    return x
+
+
+def compact_sweep(entries):
+    """48 dicts (~46 KB) -> one table (~1.8 KB).  groups["mass_f64"][c][i] is column SWEEP_COLS[c] at degree P[i]:
+    median fraction of the measured HBM peak, worst-placement fraction, median GDoF/s, spot-check error / tolerance,
+    median SM MHz; 3 significant digits.  Group names: mass | stiffness (REF_EXACT) | stiffness_full, then the dtype."""
+    groups = {}
+    for e in sorted(entries, key=lambda e: e["degree"]):
+        g = groups.setdefault(e["name"].replace(f"_P{e['degree']}_", "_"), {"P": [], "v": [[] for _ in SWEEP_COLS]})
+        mhz = (e.get("clocks") or {}).get("sm_mhz")
+        row = sig([e["frac"], e["frac_min"], e["gdofs"]["median"], e["max_rel_err"] / e["tol"],
+                   float(mhz) if mhz is not None else None], 3)
+        g["P"].append(e["degree"])
+        row[-1] = int(row[-1]) if row[-1] is not None else None
+        for col, v in zip(g["v"], row):
+            col.append(v)
+    degrees = [g["P"] for g in groups.values()]
+    if degrees and all(d == degrees[0] for d in degrees):
+        return {"cols": SWEEP_COLS, "P": degrees[0], "groups": {k: g["v"] for k, g in groups.items()}}
+    return {"cols": SWEEP_COLS, "groups": groups}
+
+
+def _pick(d, keys):
+    return {k: d[k] for k in keys if isinstance(d, dict) and k in d}
+
+
+def slim_line(line):
+    """The printed form of a full bench record: every contract key kept (value, roofline, e2e, cpu_baseline, clocks,
+    strong, ...), prose and per-entry detail dropped, floats at 6 significant digits (checksums keep all digits)."""
+    out = dict(line)
+    if isinstance(out.get("roofline"), dict):
+        out["roofline"] = {k: v for k, v in out["roofline"].items() if k != "stream_peak_note"}
+    if isinstance(out.get("e2e"), dict) and isinstance(out["e2e"].get("copy_bound"), dict):
+        out["e2e"] = dict(out["e2e"])
+        out["e2e"]["copy_bound"] = _pick(out["e2e"]["copy_bound"], ("ms_per_step", "h2d_gbs", "value_at_bound",
+                                                                     "pipeline_efficiency"))
+    if isinstance(out.get("strong"), dict):
+        st = out["strong"]
+        slim = _pick(st, ("value", "unit", "scaling", "n_gpus", "steps", "warmup", "ms_per_step", "dtype", "gpu_launches"))
+        slim["config"] = _pick(st.get("config", {}), ("workload", "total_cells", "chunks_per_rank"))
+        slim["roofline"] = _pick(st.get("roofline", {}), ("achieved", "peak", "frac"))
+        slim["clocks"] = _pick(st.get("clocks", {}), ("sm_mhz", "sm_max_mhz", "reasons"))
+        slim["parity"] = _pick(st.get("parity", {}), ("max_rel_err", "tol", "ok"))
+        out["strong"] = slim
+    if isinstance(out.get("sweep"), list):
+        out["sweep"] = compact_sweep(out["sweep"])
+    if isinstance(out.get("sweep_summary"), dict):
+        out["sweep_summary"] = {k: v for k, v in out["sweep_summary"].items() if k not in ("timing", "peak_source")}
+    cb = out.get("cpu_baseline")
+    if isinstance(cb, dict):
+        cb = dict(cb)
+        if isinstance(cb.get("tuning"), dict):
+            cb["tuning"] = _pick(cb["tuning"], ("one_core_best", "one_core_best_gdofs"))
+        if isinstance(cb.get("cache_resident"), dict):
+            cb["cache_resident"] = _pick(cb["cache_resident"], ("value", "unit", "cores"))
+        out["cpu_baseline"] = cb
+    checksum = out.get("checksum")
+    out = sig(out)
+    if checksum is not None:
+        out["checksum"] = checksum
+    return out
+
+
+# optional keys given up (in this order) if a line would still exceed LINE_LIMIT; contract keys are never touched
+DROP_ORDER = ("other_mode", "checksum", "sweep", "strong", "e2e_resident_geometry", "sweep_summary", "leg_errors")
+
+
+def fit_line(line, limit=LINE_LIMIT):
+    line = dict(line)
+    dropped = []
+    for key in DROP_ORDER:
+        if len(json.dumps(line)) <= limit:
+            break
+        if key in line:
+            del line[key]
+            dropped.append(key)
+            line["dropped_for_size"] = dropped
+    return line
+
+
+def write_detail(a, world, line):
+    """Full record (per-entry sweep detail, CPU tuning table, notes) next to the run; never fatal."""
+    path = Path(a.detail_file) if a.detail_file else ROOT / "gpurun_out" / f"bench_detail_n{world}.json"
+    try:
+        path.parent.mkdir(parents=True, exist_ok=True)
+        path.write_text(json.dumps(line, indent=1) + "\n")
+        return str(path.relative_to(ROOT)) if path.is_relative_to(ROOT) else str(path)
+    except OSError:
+        return None
+
+
 def run_ours(a, rank: int, local_rank: int, world: int):
     import torch
     import torch.distributed as dist
@@ -696,7 +806,7 @@ def run_ours(a, rank: int, local_rank: int, world: int):
         K.destroy()
         del hU, hG, hW
 
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+    if rank == 0 and not a.no_cpu_baseline:
         W_main_head = W[:min(cells, 262144) * nd].cpu().numpy()
 
     # ---- secondary figure: the other stiffness mode, same inputs ---------------------------------------------
@@ -792,7 +902,7 @@ def run_ours(a, rank: int, local_rank: int, world: int):
                       "mass P=1 fp32 (96 MB)"}
     if leg_errors:
         line["leg_errors"] = leg_errors
-    if world == 1 and not a.no_cpu_baseline:
+    if not a.no_cpu_baseline:  # rank 0, at every N (the other ranks wait at the final barrier)
         try:
             threads = os.cpu_count() or 1
             triple, tuning = cpu_tuning(a)
@@ -814,7 +924,11 @@ def run_ours(a, rank: int, local_rank: int, world: int):
         except Exception as exc:  # noqa: BLE001  (the CPU leg must not cost the GPU line)
             line["cpu_baseline"] = {"value": None, "unit": "GDoF/s", "cores": os.cpu_count() or 1, "kind": "unavailable",
                                     "sample": f"{type(exc).__name__}: {exc}"}
-    print(json.dumps(line), flush=True)
+    detail = write_detail(a, world, line)
+    printed = slim_line(line)
+    if detail:
+        printed["detail_file"] = detail
+    print(json.dumps(fit_line(printed)), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

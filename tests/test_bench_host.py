@@ -66,3 +66,42 @@ def test_sweep_front_end_prints_the_reference_report_line():
     e = {"op": "mass", "degree": 2, "dtype": "f32", "cells": 10, "ms": {"median": 1.0}}
     f = mod.reference_line(e).split()
     assert f[2] == "float" and abs(float(f[9]) - 4 * 270 * 4 / 1e-3 / 1e9) < 1e-9
+
+
+def test_the_printed_line_stays_small_and_keeps_every_contract_key():
+    """Round 2's N = 1 line was 52 KB (48 sweep dicts inside it) and the driver's capture held only its tail.  The
+    printed form of that very record (profiles/r02_bench_n1.json) must fit in 6 KB with value / roofline / e2e /
+    cpu_baseline / clocks / strong and a compact sweep table still in it, and fit_line must bound any record."""
+    import json
+    b = load_bench()
+    full = json.loads((ROOT / "profiles" / "r02_bench_n1.json").read_text())
+    assert len(json.dumps(full)) > 40_000 and len(full["sweep"]) == 48
+    full["leg_errors"] = {"stream_peaks": "RuntimeError: " + "x" * 120}
+    line = b.slim_line(full)
+    line["detail_file"] = "gpurun_out/bench_detail_n1.json"
+    printed = b.fit_line(line)
+    text = json.dumps(printed)
+    assert len(text) < 6144, len(text)
+    assert "dropped_for_size" not in printed
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "roofline", "e2e", "gpu_launches", "clocks", "cpu_baseline",
+                "strong", "sweep", "sweep_summary"):
+        assert key in printed, key
+    assert printed["config"] == full["config"]                       # both arms print the same config
+    for key in ("bound", "achieved", "peak", "unit", "frac", "traffic"):
+        assert key in printed["roofline"]
+    for key in ("value", "unit", "cores", "kind", "sample"):
+        assert key in printed["cpu_baseline"]
+    for key in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"):
+        assert key in printed["e2e"]
+    assert abs(printed["value"] / full["value"] - 1) < 1e-5 and printed["checksum"] == full["checksum"]
+    sw = printed["sweep"]
+    assert sw["P"] == list(range(1, 9)) and len(sw["groups"]) == 6 and sw["cols"][0] == "frac"
+    e = next(x for x in full["sweep"] if x["name"] == "stiffness_P3_f64")
+    assert abs(sw["groups"]["stiffness_f64"][0][2] / e["frac"] - 1) < 5e-3
+    # the guard: a record that is still too large loses optional keys, never contract keys
+    line["sweep_summary"]["junk"] = "y" * 5000
+    small = b.fit_line(line)
+    assert len(json.dumps(small)) < 6144 and "dropped_for_size" in small
+    for key in ("value", "roofline", "e2e", "cpu_baseline", "clocks", "config"):
+        assert key in small
