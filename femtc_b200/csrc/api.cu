@@ -79,6 +79,7 @@ static long long env_int(const char* name, long long lo, long long hi, long long
   return x < lo || x > hi ? dflt : x;
 }
 static std::atomic<long long> g_opt_host_devices{env_int("FEMTC_HOST_DEVICES", 1, 64, 1)};
+static std::atomic<long long> g_opt_host_oversubscribe{env_int("FEMTC_HOST_DEVICES_OVERSUBSCRIBE", 0, 1, 0)};
 static std::atomic<long long> g_opt_tc{env_int("FEMTC_TC", -1, 1, -1)}; // env: initial value of option "tc" (A/B runs of whole programs)
 
 long long opt_variant() { return g_opt_variant.load(); }
@@ -365,6 +366,9 @@ static int ensure(void*& p, size_t& cap, size_t bytes)
 // drop-in library cannot know about.
 static std::mutex g_reg_mu;
 static std::map<uintptr_t, size_t> g_registered; // base -> bytes
+// host-pointer calls between their registration step and their return (guarded by g_reg_mu): while any is in flight no
+// registration is dropped, because its copies may be running through it (another thread's call on an overlapping slice)
+static int g_host_calls_in_flight = 0;
 
 static bool page_locked(const void* p)
 {
@@ -377,13 +381,13 @@ static bool page_locked(const void* p)
   return attr.type != cudaMemoryTypeUnregistered;
 }
 
+// caller holds g_reg_mu
 static void maybe_register(const void* ptr, size_t bytes)
 {
   if (!g_opt_host_register.load() || !ptr || bytes < (size_t(1) << 20))
     return;
   const uintptr_t base = reinterpret_cast<uintptr_t>(ptr), end = base + bytes;
   static const bool debug = env_flag("FEMTC_DEBUG_REGISTER"); // development: log every decision on stderr
-  std::lock_guard<std::mutex> lock(g_reg_mu);
   // One of our own registrations that covers the range: done.  One that only overlaps it is stale (the caller
   // freed the buffer and got the address again with another size) or too short: drop it and register afresh.
   for (auto it = g_registered.begin(); it != g_registered.end();)
@@ -397,6 +401,13 @@ static void maybe_register(const void* ptr, size_t bytes)
     }
     if (b < end && base < e)
     {
+      if (g_host_calls_in_flight > 0)
+      {
+        // another call may be copying through that entry right now: leave it, serve this range pageable this time
+        if (debug)
+          std::fprintf(stderr, "femtc_b200: %p +%zu overlaps own entry %p +%zu in use: left alone\n", ptr, bytes, (void*)b, it->second);
+        return;
+      }
       if (debug)
         std::fprintf(stderr, "femtc_b200: %p +%zu overlaps own entry %p +%zu: dropping it\n", ptr, bytes, (void*)b, it->second);
       if (cudaHostUnregister(reinterpret_cast<void*>(b)) != cudaSuccess)
@@ -520,27 +531,45 @@ template <typename T, typename Launch>
 static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t num_cells, size_t nd,
                          Launch&& launch, const T* geom_dev = nullptr)
 {
-  maybe_register(U, num_cells * nd * sizeof(T));
-  maybe_register(W, num_cells * nd * sizeof(T));
-  if (!geom_dev)
-    maybe_register(geom, num_cells * nd * geom_width * sizeof(T));
+  struct InFlight // registration step and in-flight count under one lock; the count is given back on every exit
+  {
+    InFlight(const T* U, T* W, const T* geom, size_t bU, size_t bG)
+    {
+      std::lock_guard<std::mutex> lock(g_reg_mu);
+      maybe_register(U, bU);
+      maybe_register(W, bU);
+      if (geom)
+        maybe_register(geom, bG);
+      ++g_host_calls_in_flight;
+    }
+    ~InFlight()
+    {
+      std::lock_guard<std::mutex> lock(g_reg_mu);
+      --g_host_calls_in_flight;
+    }
+  } in_flight(U, W, geom_dev ? nullptr : geom, num_cells * nd * sizeof(T), num_cells * nd * geom_width * sizeof(T));
   const size_t kCutCells = cut_cells(nd);
-  int ndev = (int)std::min<long long>(g_opt_host_devices.load(), g_usable_devices);
-  if (geom_dev || ndev < 2 || num_cells < (size_t)ndev * kCutCells)
+  // option "host_devices_oversubscribe" / FEMTC_HOST_DEVICES_OVERSUBSCRIBE=1 (testing on a box with fewer GPUs than shares): the share count is not clamped
+  // and share r runs on device r % visible; shares of one device take turns on its pipeline
+  const bool oversubscribe = g_opt_host_oversubscribe.load() != 0;
+  const int visible = g_usable_devices;
+  int ndev = (int)(oversubscribe ? g_opt_host_devices.load() : std::min<long long>(g_opt_host_devices.load(), visible));
+  if (geom_dev || ndev < 2 || visible < 1 || num_cells < (size_t)ndev * kCutCells)
     return host_pipeline_device<T>(U, W, geom, geom_width, num_cells, nd, launch, geom_dev);
 
-  int home = 0;
-  FEMTC_CUDA(cudaGetDevice(&home));
   std::vector<int> rcs(ndev, FEMTC_OK);
   std::vector<std::string> errs(ndev);
   std::vector<std::thread> workers;
   auto cut = [&](int r) { return r == ndev ? num_cells : (num_cells * r / ndev) / kCutCells * kCutCells; };
-  for (int r = 0; r < ndev; ++r)
+  bool spawn_failed = false;
+  for (int r = 0; r < ndev && !spawn_failed; ++r)
   {
     const size_t c0 = cut(r), c1 = cut(r + 1);
-    workers.emplace_back([&, r, c0, c1]
+    try
     {
-      cudaError_t e = cudaSetDevice(r);
+      workers.emplace_back([&, r, c0, c1]
+    {
+      cudaError_t e = cudaSetDevice(r % visible);
       if (e != cudaSuccess)
       {
         rcs[r] = cuda_fail(e, "cudaSetDevice(host_devices share)", __FILE__, __LINE__);
@@ -551,9 +580,19 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
       if (rcs[r])
         errs[r] = t_last_error; // the error text is thread-local: hand it to the caller's thread
     });
+    }
+    catch (const std::exception&) // thread creation failed: the workers already started are joined below
+    {
+      spawn_failed = true;
+    }
   }
   for (auto& w : workers)
     w.join();
+  if (spawn_failed)
+  {
+    set_error("host_devices: could not start a worker thread");
+    return FEMTC_ERR_CUDA;
+  }
   for (int r = 0; r < ndev; ++r)
     if (rcs[r])
     {
@@ -1272,6 +1311,8 @@ int femtc_set_option(const char* name, long long value)
     g_opt_host_register = value;
   else if (!std::strcmp(name, "host_devices") && value >= 1 && value <= 64)
     g_opt_host_devices = value;
+  else if (!std::strcmp(name, "host_devices_oversubscribe") && (value == 0 || value == 1))
+    g_opt_host_oversubscribe = value;
   else if (!std::strcmp(name, "variant"))
     g_opt_variant = value;
   else if (!std::strcmp(name, "tc") && value >= -1 && value <= 1)
@@ -1295,6 +1336,8 @@ long long femtc_get_option(const char* name)
     return g_opt_host_register;
   if (!std::strcmp(name, "host_devices"))
     return g_opt_host_devices;
+  if (!std::strcmp(name, "host_devices_oversubscribe"))
+    return g_opt_host_oversubscribe;
   if (!std::strcmp(name, "variant"))
     return g_opt_variant;
   if (!std::strcmp(name, "tc"))

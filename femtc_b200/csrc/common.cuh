@@ -69,8 +69,9 @@ inline void note_launch(int family, int detail, K kernel, int cells_per_tile, in
     {                                                                                                           \
       kernel<<<grid, threads, smem, stream>>>(__VA_ARGS__);                                                     \
       ::femtc::count_launch();                                                                                  \
-      if (cudaGetLastError() != cudaSuccess)                                                                    \
-        return -FEMTC_ERR_CUDA;                                                                                 \
+      const cudaError_t le__ = cudaGetLastError();                                                              \
+      if (le__ != cudaSuccess)                                                                                  \
+        return -::femtc::cuda_fail(le__, "launch of " #kernel, __FILE__, __LINE__);                             \
     }                                                                                                           \
   } while (0)
 

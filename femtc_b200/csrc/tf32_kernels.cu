@@ -213,8 +213,10 @@ __global__ void __launch_bounds__(128) mass_tf32_kernel(const __grid_constant__ 
                                                         float* __restrict__ W, const float* __restrict__ detJ,
                                                         long long ntiles)
 {
+  // CUDA promises 16-byte alignment of the dynamic shared-memory base, nothing more; the SWIZZLE_128B operand
+  // descriptors below are built with base offset 0 and need 1024: round up here (the launch asks for 1 KB of slack)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  Tf32Smem& s = *reinterpret_cast<Tf32Smem*>(smem_raw);
+  Tf32Smem& s = *reinterpret_cast<Tf32Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x;
 
   if (tid < 64) // B[k = p][n = i] = A(i, p) = phi[i + p n1] (mass.hpp:20-21), as K-major core matrices (8 n x 16 bytes)
@@ -338,7 +340,7 @@ long long launch_mass_tf32(const MassArgs<float>& a)
   for (int i = 0; i < TN1 * TN1; ++i)
     B.a[i] = a.phi_host[i];
   auto kernel = mass_tf32_kernel;
-  constexpr size_t smem = sizeof(Tf32Smem);
+  constexpr size_t smem = sizeof(Tf32Smem) + 1024; // + slack for the in-kernel round-up of the base to 1024 bytes
   static std::mutex mu;
   static std::map<int, int> plans; // device -> resident blocks per SM
   int dev = 0, bps = 0;

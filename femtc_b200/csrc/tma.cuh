@@ -30,6 +30,18 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
 //      mbarrier.arrive (release.cta: the lane's prior shared-memory reads are performed before the arrival, and the
 //      arrival is queued behind them in the same in-order shared-memory pipe), and the lanes that issue the refill
 //      wait (acquire) for the phase, i.e. for all arrivals, before cp.async.bulk.  slot_release_and_acquire() below.
+//  (2') block-wide rings filled by a producer warp (column_kernels.cu, PW; the n1 >= 7 stiffness defaults) hand a slot back
+//      with `__syncwarp(); if (lane == 0) mbar_arrive(empty)` and an `empty` count of one arrival per compute warp.  That
+//      is rule 2 with one arrival standing for the warp, and it is sufficient there because the refill is issued by
+//      ANOTHER warp behind an acquire: (a) __syncwarp orders every lane's earlier shared-memory reads before anything
+//      lane 0 does after it, (b) lane 0's arrive is a release and release is cumulative, so those reads are performed
+//      before the producer's try_wait (acquire) can observe the completed phase, and only then does the producer issue
+//      the bulk copy; (c) in the pipe, the warp's loads are warp-wide instructions issued before the arrive instruction
+//      of the same converged warp, so the arrival cannot be queued ahead of another lane's load.  The round-1 failure had
+//      no such hand-over (loads, __syncwarp, fence and the refill all in one warp, nothing waiting on an arrival).
+//      The form is the consumer release of CUTLASS's TMA pipelines (one elected arrive per consumer warp).  Evidence for
+//      these kernels specifically: tests/test_gpu_parity.py::test_repeated_launches_on_cache_resident_fields_are_bit_identical runs the
+//      default fp32 REF_EXACT stiffness kernels at n1 = 7 and 9 (block-wide rings) 1000 times against their first result.
 #ifndef FEMTC_RELEASE_LANES
 #define FEMTC_RELEASE_LANES 32 // arrivals per warp on an `empty` barrier (32: every reading lane; 1: lane 0 after __syncwarp, A/B only)
 #endif

@@ -269,6 +269,11 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
  *                     the unchanged drivers (bench_stiffness.cpp:95-105) move their fields over n PCIe links.  The
  *                     action is cell-local: the result is bit-identical to the one-device call.  Default 1, or
  *                     FEMTC_HOST_DEVICES from the environment at load time; clamped to the visible devices.
+ *                     Every process that inherits the variable opens contexts on devices 0..n-1: leave it unset under
+ *                     a one-rank-per-GPU launcher (mpirun, torchrun), where each rank already owns a device.
+ *   "host_devices_oversubscribe"  1: the share count is not clamped and share r runs on device r % visible -- lets a
+ *                     one-GPU box exercise the fan-out (cut points, worker threads, error hand-over).  Default 0, or
+ *                     FEMTC_HOST_DEVICES_OVERSUBSCRIBE from the environment.
  *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
  *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
  *   "variant"         development knob for A/B measurements (0 = tuned defaults).  1, 2: alternative pipeline
