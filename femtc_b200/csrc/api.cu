@@ -602,6 +602,113 @@ static int host_pipeline(const T* U, T* W, const T* geom, int geom_width, size_t
   return FEMTC_OK;
 }
 
+// ---- opt-in geometry cache behind the drop-in host-pointer call ----------------------------------
+// The unchanged drivers apply the operator nreps times to the SAME detJ / G (bench_mass.cpp:95-105,
+// bench_stiffness.cpp:95-105), and the geometry is 1 of 3 (mass) or 6 of 8 (stiffness) words per DoF that cross PCIe on
+// every call.  With option "geom_cache" = 1 (FEMTC_GEOM_CACHE=1) the host-pointer entry points keep the geometry array
+// in HBM, keyed by (device, host address, bytes) and guarded by a 64-bit hash of 4 KB sampled at fixed strides: a later
+// call with the same key and hash moves only U in and W out (the ResidentOperator path, same kernels, same chunk cuts:
+// bit-identical).  A changed hash re-uploads; femtc_release_cache() drops everything.  OFF by default: a drop-in
+// library cannot know that the caller rewrote geometry between calls in a place the samples miss -- a caller who
+// does that must call femtc_release_cache() (or leave the option off).
+static std::atomic<long long> g_opt_geom_cache{env_int("FEMTC_GEOM_CACHE", 0, 1, 0)};
+static std::atomic<long long> g_geom_uploads{0};
+struct GeomEntry
+{
+  int device;
+  const void* host;
+  size_t bytes;
+  uint64_t hash;
+  void* dev;
+};
+static std::mutex g_geom_mu;
+static std::vector<GeomEntry> g_geom;
+
+static uint64_t sampled_hash(const void* p, size_t bytes)
+{
+  // 64 blocks of 64 bytes, first block at 0, last block ending at the last whole word; 8-byte words through splitmix64
+  const unsigned char* b = static_cast<const unsigned char*>(p);
+  const size_t words = bytes / 8;
+  uint64_t h = splitmix64(bytes);
+  if (words == 0)
+    return h;
+  const size_t blocks = 64, per = 8;
+  for (size_t i = 0; i < blocks; ++i)
+  {
+    const size_t w0 = words <= per ? 0 : (size_t)((long double)(words - per) * i / (blocks - 1));
+    for (size_t k = 0; k < per && w0 + k < words; ++k)
+    {
+      uint64_t v;
+      std::memcpy(&v, b + (w0 + k) * 8, 8);
+      h = splitmix64(h ^ v);
+    }
+  }
+  return h;
+}
+
+// Device copy of `geom` on the current device, or nullptr when the cache is off / cannot hold it (the caller then takes
+// the strict path; never an error).
+static const void* cached_geometry(const void* geom, size_t bytes)
+{
+  if (!g_opt_geom_cache.load() || !geom || bytes == 0)
+    return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess)
+    return nullptr;
+  const uint64_t h = sampled_hash(geom, bytes);
+  std::lock_guard<std::mutex> lock(g_geom_mu);
+  GeomEntry* e = nullptr;
+  for (auto& g : g_geom)
+    if (g.device == dev && g.host == geom && g.bytes == bytes)
+      e = &g;
+  if (e && e->hash == h)
+    return e->dev;
+  if (!e)
+  {
+    void* d = nullptr;
+    if (cudaMalloc(&d, bytes) != cudaSuccess)
+    {
+      (void)cudaGetLastError(); // no room in HBM for a resident copy: strict path
+      return nullptr;
+    }
+    g_geom.push_back({dev, geom, bytes, 0, d});
+    e = &g_geom.back();
+  }
+  if (cudaMemcpy(e->dev, geom, bytes, cudaMemcpyHostToDevice) != cudaSuccess)
+  {
+    (void)cudaGetLastError();
+    cudaFree(e->dev);
+    g_geom.erase(g_geom.begin() + (e - g_geom.data()));
+    return nullptr;
+  }
+  e->hash = h;
+  g_geom_uploads.fetch_add(1);
+  return e->dev;
+}
+
+static void drop_cached_geometry()
+{
+  std::lock_guard<std::mutex> lock(g_geom_mu);
+  int cur = 0;
+  const bool have = cudaGetDevice(&cur) == cudaSuccess;
+  for (auto& g : g_geom)
+  {
+    cudaSetDevice(g.device);
+    cudaFree(g.dev);
+  }
+  g_geom.clear();
+  if (have)
+    cudaSetDevice(cur);
+}
+
+// one device serves the call and the geometry may stay resident there
+static bool geometry_cacheable()
+{
+  const long long shares = g_opt_host_oversubscribe.load() ? g_opt_host_devices.load()
+                                                           : std::min<long long>(g_opt_host_devices.load(), g_usable_devices);
+  return g_opt_geom_cache.load() && shares < 2;
+}
+
 template <typename T>
 static int mass_host(const T* phi, size_t phi_len, const T* U, T* W, const T* detJ, size_t num_cells,
                      int degree, int order, int Mb, int Nb)
@@ -625,9 +732,12 @@ static int mass_host(const T* phi, size_t phi_len, const T* U, T* W, const T* de
     return rc;
   if (num_cells == 0)
     return FEMTC_OK;
-  return host_pipeline<T>(U, W, detJ, 1, num_cells, n1 * n1 * n1,
+  const T* resident = geometry_cacheable()
+                          ? static_cast<const T*>(cached_geometry(detJ, num_cells * n1 * n1 * n1 * sizeof(T))) : nullptr;
+  return host_pipeline<T>(U, W, resident ? (const T*)nullptr : detJ, 1, num_cells, n1 * n1 * n1,
                           [&](const T* dU, T* dW, const T* dJ, size_t n, cudaStream_t s)
-                          { return mass_device<T>(phi, phi_len, dU, dW, dJ, n, degree, s); });
+                          { return mass_device<T>(phi, phi_len, dU, dW, dJ, n, degree, s); },
+                          resident);
 }
 
 template <typename T>
@@ -658,9 +768,12 @@ static int stiffness_host(const T* phi, size_t phi_len, const T* U, T* W, const 
     return rc;
   if (num_cells == 0)
     return FEMTC_OK;
-  return host_pipeline<T>(U, W, G, 6, num_cells, n1 * n1 * n1,
+  const T* resident = geometry_cacheable()
+                          ? static_cast<const T*>(cached_geometry(G, num_cells * n1 * n1 * n1 * 6 * sizeof(T))) : nullptr;
+  return host_pipeline<T>(U, W, resident ? (const T*)nullptr : G, 6, num_cells, n1 * n1 * n1,
                           [&](const T* dU, T* dW, const T* dG, size_t n, cudaStream_t s)
-                          { return stiffness_device<T>(phi, phi_len, dU, dW, dG, n, degree, mode, s); });
+                          { return stiffness_device<T>(phi, phi_len, dU, dW, dG, n, degree, mode, s); },
+                          resident);
 }
 
 // ---- small host-pointer helpers for the GEMM / contraction entry points ----------------------------
@@ -1272,6 +1385,7 @@ void femtc_host_free(void* p)
 void femtc_release_cache(void)
 {
   unregister_all();
+  drop_cached_geometry();
   int cur = 0;
   if (g_usable_devices <= 0 || cudaGetDevice(&cur) != cudaSuccess)
     return;
@@ -1313,6 +1427,8 @@ int femtc_set_option(const char* name, long long value)
     g_opt_host_devices = value;
   else if (!std::strcmp(name, "host_devices_oversubscribe") && (value == 0 || value == 1))
     g_opt_host_oversubscribe = value;
+  else if (!std::strcmp(name, "geom_cache") && (value == 0 || value == 1))
+    g_opt_geom_cache = value;
   else if (!std::strcmp(name, "variant"))
     g_opt_variant = value;
   else if (!std::strcmp(name, "tc") && value >= -1 && value <= 1)
@@ -1338,6 +1454,10 @@ long long femtc_get_option(const char* name)
     return g_opt_host_devices;
   if (!std::strcmp(name, "host_devices_oversubscribe"))
     return g_opt_host_oversubscribe;
+  if (!std::strcmp(name, "geom_cache"))
+    return g_opt_geom_cache;
+  if (!std::strcmp(name, "geom_cache_uploads"))
+    return g_geom_uploads;
   if (!std::strcmp(name, "variant"))
     return g_opt_variant;
   if (!std::strcmp(name, "tc"))

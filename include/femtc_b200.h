@@ -274,6 +274,14 @@ void femtc_release_cache(void);           /* drop cached device staging buffers 
  *   "host_devices_oversubscribe"  1: the share count is not clamped and share r runs on device r % visible -- lets a
  *                     one-GPU box exercise the fan-out (cut points, worker threads, error hand-over).  Default 0, or
  *                     FEMTC_HOST_DEVICES_OVERSUBSCRIBE from the environment.
+ *   "geom_cache"      1: the host-pointer operator entry points keep detJ / G resident in HBM between calls, keyed by
+ *                     (device, host address, bytes) and checked against a 64-bit hash of 4 KB sampled across the array;
+ *                     a repeat call (bench_stiffness.cpp:95-105 applies the operator to the same G every repetition)
+ *                     then moves only U in and W out -- same kernels, bit-identical.  A hash mismatch re-uploads;
+ *                     femtc_release_cache() frees the copies.  A caller that rewrites geometry in place between calls
+ *                     must call femtc_release_cache() (the samples can miss a local change) or leave this off.  Not
+ *                     combined with "host_devices" > 1.  Default 0, or FEMTC_GEOM_CACHE from the environment.
+ *   "geom_cache_uploads"  (read-only) geometry uploads the cache has made so far
  *   "tc"              DMMA tensor-core family (fp64, degrees 5..8, mass / REF_EXACT): -1 = where it is
  *                     measured faster than the FMA kernels (default), 0 = never, 1 = wherever applicable
  *   "variant"         development knob for A/B measurements (0 = tuned defaults).  1, 2: alternative pipeline

@@ -211,6 +211,41 @@ def test_host_register_grows_with_a_larger_buffer_at_the_same_address(femtc, ora
     assert not torch.from_numpy(geom).is_pinned()
 
 
+@pytest.mark.parametrize("op,mode,P,dt", [("stiffness", 0, 3, "float64"), ("mass", 0, 4, "float32"), ("stiffness", 1, 6, "float32")])
+def test_geometry_cache_behind_the_drop_in_call(femtc, oracle, op, mode, P, dt):
+    """Option "geom_cache" = 1: the unchanged host-pointer call keeps detJ / G in HBM between calls
+    (bench_stiffness.cpp:95-105 re-applies the operator to the same G).  A repeat call uploads nothing and is
+    bit-identical to the strict call; geometry rewritten in place is noticed through the sampled hash and uploaded again;
+    femtc_release_cache() forgets everything."""
+    nc = 16 * 96 * 5 + 16 * 3
+    phi, U, geom = splitmix(oracle, op, P, nc, dt, seed=13)
+    strict = run_host(femtc, op, phi, U, geom, P, mode)
+    uploads = lambda: femtc.get_option("geom_cache_uploads")
+    femtc.set_option("geom_cache", 1)
+    femtc.set_option("host_chunk_mb", 1)
+    try:
+        n0 = uploads()
+        first = run_host(femtc, op, phi, U, geom, P, mode)
+        assert uploads() == n0 + 1 and np.array_equal(first, strict)
+        U2 = np.ascontiguousarray(U[::-1])                       # new field, same geometry: nothing uploaded
+        again = run_host(femtc, op, phi, U2, geom, P, mode)
+        assert uploads() == n0 + 1
+        femtc.set_option("geom_cache", 0)
+        assert np.array_equal(again, run_host(femtc, op, phi, U2, geom, P, mode))
+        femtc.set_option("geom_cache", 1)
+        geom *= geom.dtype.type(1.25)                            # rewritten in place: same address, other content
+        changed = run_host(femtc, op, phi, U, geom, P, mode)
+        assert uploads() == n0 + 2
+        assert elementwise_rel_err(changed, oracle_run(oracle, op, phi, U, geom, P, mode)) <= TOL[dt]
+        femtc._lib.lib.femtc_release_cache()
+        run_host(femtc, op, phi, U, geom, P, mode)
+        assert uploads() == n0 + 3
+    finally:
+        femtc.set_option("geom_cache", 0)
+        femtc.set_option("host_chunk_mb", 64)
+        femtc._lib.lib.femtc_release_cache()
+
+
 @pytest.mark.parametrize("op,mode,P,dt", [("stiffness", 0, 3, "float64"), ("mass", 0, 4, "float32"), ("stiffness", 1, 6, "float64")])
 def test_one_host_call_fanned_out_over_all_devices(femtc, oracle, op, mode, P, dt):
     """Option "host_devices" = n: one host-pointer call is cut into n contiguous cell ranges, one per device; the

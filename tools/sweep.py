@@ -3,7 +3,11 @@
 (degree x loop-order sweep of ./build/gemm_order) and of the one-line report of bench_mass.cpp:118-146.
 
     python tools/sweep.py [--filter stiffness_P] [--cells 1000000] [--csv out.csv] [--json out.json]
-    python tools/sweep.py --from-json BENCH.json       # re-print a recorded bench.py line, no GPU needed
+    python tools/sweep.py --from-json RECORD.json      # re-print a recorded full bench.py record, no GPU needed
+    python tools/sweep.py --from-json RECORD.json --markdown   # the DESIGN.md section 5 table, generated, never typed
+
+RECORD.json is the full record bench.py writes next to its compact stdout line (gpurun_out/bench_detail_n1.json, committed
+copies under profiles/), or a round-2 line that still carried the 48 entries itself.
 
 Runs bench.py's `sweep` leg (48 entries: mass / stiffness REF_EXACT / stiffness FULL x P = 1..8 x fp64 / fp32; per entry
 five placements, clocks, oracle spot check) and prints, per entry,
@@ -57,8 +61,36 @@ def csv_row(e):
             "blocks_per_sm": e["kernel"]["blocks_per_sm"]}
 
 
+FAMILY_TAG = {"slab": "s", "cell": "c", "column": "col", "tensor core": "tc", "generic": "g"}
+
+
+def markdown_table(sweep, peak):
+    """per degree and operator, median fraction of the measured HBM peak / of the nominal 8 TB/s,
+    and the kernel family that served the entry."""
+    cols = (("mass", "ref_exact", "f64", "mass fp64"), ("mass", "ref_exact", "f32", "mass fp32"),
+            ("stiffness", "ref_exact", "f64", "stiffness fp64"), ("stiffness", "ref_exact", "f32", "stiffness fp32"),
+            ("stiffness", "full", "f64", "FULL fp64"), ("stiffness", "full", "f32", "FULL fp32"))
+    by = {(e["op"], e["mode"], e["dtype"], e["degree"]): e for e in sweep}
+    out = [f"Median over five placements: fraction of the measured peak ({peak:.1f} GB/s) / of nominal 8 TB/s, kernel family "
+           "(s slab, c cell, col column, tc tensor core).", "",
+           "| P | " + " | ".join(c[3] for c in cols) + " |", "|---|" + "---|" * len(cols)]
+    for P in sorted({e["degree"] for e in sweep}):
+        cells = []
+        for op, mode, dt, _ in cols:
+            e = by.get((op, mode, dt, P))
+            cells.append("–" if e is None else f"{e['frac']:.2f} / {e['frac_of_nominal_8TBs']:.2f} {FAMILY_TAG.get(e['family'], e['family'])}")
+        out.append(f"| {P} | " + " | ".join(cells) + " |")
+    fr = sorted(e["frac"] for e in sweep)
+    low = [e["frac"] for e in sweep if e["degree"] <= 4 and e["mode"] == "ref_exact"]
+    out += ["", f"Entries {len(sweep)}, parity ok {sum(1 for e in sweep if e['parity_ok'])}; median of all {fr[len(fr) // 2 - 1] / 2 + fr[len(fr) // 2] / 2:.3f}"
+            if len(fr) % 2 == 0 else f"Entries {len(sweep)}; median {fr[len(fr) // 2]:.3f}",
+            f"minimum over mass / REF_EXACT at degree <= 4: {min(low):.3f} of measured, {min(low) * peak / 8000:.3f} of 8 TB/s." if low else ""]
+    return "\n".join(out)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--markdown", action="store_true", help="print the DESIGN.md section 5 table instead of the report lines")
     ap.add_argument("--filter", default="")
     ap.add_argument("--cells", type=int, default=1_000_000)
     ap.add_argument("--csv")
@@ -66,14 +98,23 @@ def main():
     ap.add_argument("--from-json", help="print from a recorded bench.py JSON line instead of running")
     a = ap.parse_args()
     if a.from_json:
-        line = json.loads(Path(a.from_json).read_text().strip().splitlines()[-1])
+        text = Path(a.from_json).read_text().strip()
+        try:
+            line = json.loads(text)                          # a full record (indented or one line)
+        except json.JSONDecodeError:
+            line = json.loads(text.splitlines()[-1])         # a log whose last line is the record
         line = line.get("parsed", line)
     else:
+        # bench.py prints a compact line; the 48 full entries are in the record it writes beside it
+        detail = ROOT / "gpurun_out" / "sweep_tool_detail.json"
         cmd = [sys.executable, str(ROOT / "bench.py"), "--steps", "5", "--warmup", "3", "--no-e2e", "--no-cpu-baseline",
-               "--no-strong", "--sweep-cells", str(a.cells), "--sweep-filter", a.filter]
-        out = subprocess.run(cmd, check=True, capture_output=True, text=True).stdout
-        line = json.loads(out.strip().splitlines()[-1])
+               "--no-strong", "--sweep-cells", str(a.cells), "--sweep-filter", a.filter, "--detail-file", str(detail)]
+        subprocess.run(cmd, check=True, capture_output=True, text=True)
+        line = json.loads(detail.read_text())
     sweep = [e for e in line["sweep"] if a.filter in e["name"]]
+    if a.markdown:
+        print(markdown_table(sweep, line["roofline"]["peak"]))
+        return 0
     print("# degree size type Ndofs elapsed order Mb Nb GFLOP/s GB/s GDoF/s   (bench_mass.cpp:140-146)")
     for e in sweep:
         print(reference_line(e), f"  # {e['name']}: {e['family']}, {e['frac']:.3f} of measured HBM "
