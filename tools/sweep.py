@@ -61,7 +61,7 @@ def csv_row(e):
             "blocks_per_sm": e["kernel"]["blocks_per_sm"]}
 
 
-FAMILY_TAG = {"slab": "s", "cell": "c", "column": "col", "tensor core": "tc", "generic": "g"}
+FAMILY_TAG = {"slab": "s", "cell": "c", "column": "col", "tensor core": "tc", "tensor-core": "tc", "generic": "g"}
 
 
 def markdown_table(sweep, peak):
