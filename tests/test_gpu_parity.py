@@ -646,7 +646,11 @@ def test_device_generator_and_checksum_match_host(femtc, oracle, torch_cuda, dt)
 # ---- full-size properties (BASELINE.json configs 2 and 3 sizes) -------------------------------------------------
 @pytest.mark.parametrize("op,P,dt,mode", [("stiffness", 3, "float64", 0), ("stiffness", 3, "float64", 1),
                                           ("mass", 3, "float64", 0), ("stiffness", 4, "float32", 0),
-                                          ("mass", 8, "float32", 0)])
+                                          ("mass", 8, "float32", 0),
+                                          # round 3: the tensor-core and block-wide-ring families at full size too
+                                          # (BASELINE config 4: P=8 stiffness; DMMA mass n1 = 8; fp32 column n1 = 7)
+                                          ("stiffness", 8, "float64", 0), ("mass", 7, "float64", 0),
+                                          ("stiffness", 6, "float32", 0)])
 def test_full_size_properties(femtc, oracle, torch_cuda, op, P, dt, mode):
     """1 M cells resident in HBM: (a) spot-checks of regenerated cell ranges against the oracle,
     (b) exact linearity under power-of-two scaling, (c) chunk invariance: the action is cell-local,
